@@ -1,0 +1,119 @@
+"""TEST INFRASTRUCTURE ONLY - imports the UNMODIFIED reference hot path from /root/reference.
+
+This works only in the build container (``/root/reference`` does not exist on the GPU box), and
+is used for exactly two things: validating the restatement in ``oracle/gn_oracle.py`` and
+generating the golden vectors under ``tests/golden/`` (see ``oracle/make_golden.py``).
+Nothing in the product package imports this file.
+
+Harness steps:
+  1. stub modules for ``addict``, ``plyfile``, ``skimage.measure`` (imported at the top of
+     ``reconstruct/utils.py:21-23`` but absent here);
+  2. ``Tensor.cuda`` / ``Module.cuda`` -> identity, ``torch.cuda.synchronize/empty_cache`` -> no-op,
+     because the reference hard-codes ``.cuda()`` (``optimizer.py:120-136``, ``loss.py:32,63,84``);
+  3. ``/root/reference`` and ``/root/reference/reconstruct`` on ``sys.path`` (as ``System.cc:115-116``).
+"""
+from __future__ import annotations
+
+import os
+import sys
+import types
+import warnings
+
+REFERENCE_ROOT = "/root/reference"
+
+
+def available() -> bool:
+    return os.path.isfile(os.path.join(REFERENCE_ROOT, "reconstruct", "optimizer.py"))
+
+
+class _AttrDict(dict):
+    """Minimal stand-in for ``addict.Dict``: attribute access, nested dicts wrapped."""
+
+    def __init__(self, *a, **kw):
+        super().__init__()
+        for k, v in dict(*a, **kw).items():
+            self[k] = self._wrap(v)
+
+    @classmethod
+    def _wrap(cls, v):
+        if isinstance(v, dict) and not isinstance(v, cls):
+            return cls(v)
+        return v
+
+    def __getattr__(self, k):
+        try:
+            return self[k]
+        except KeyError:
+            return self.__missing__(k)
+
+    def __missing__(self, k):
+        v = type(self)()
+        self[k] = v
+        return v
+
+    def __setattr__(self, k, v):
+        self[k] = self._wrap(v)
+
+
+_loaded = None
+
+
+def load():
+    """Returns a namespace with the reference's modules (imported once)."""
+    global _loaded
+    if _loaded is not None:
+        return _loaded
+    if not available():
+        raise RuntimeError("/root/reference is not present on this machine")
+    import torch
+
+    addict = types.ModuleType("addict")
+    addict.Dict = _AttrDict
+    sys.modules.setdefault("addict", addict)
+    sys.modules.setdefault("plyfile", types.ModuleType("plyfile"))
+    sk = types.ModuleType("skimage")
+    skm = types.ModuleType("skimage.measure")
+    sk.measure = skm
+    sys.modules.setdefault("skimage", sk)
+    sys.modules.setdefault("skimage.measure", skm)
+
+    torch.Tensor.cuda = lambda self, *a, **k: self
+    torch.nn.Module.cuda = lambda self, *a, **k: self
+    torch.cuda.synchronize = lambda *a, **k: None
+    torch.cuda.empty_cache = lambda *a, **k: None
+
+    for p in (REFERENCE_ROOT, os.path.join(REFERENCE_ROOT, "reconstruct")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    warnings.filterwarnings("ignore")
+    import reconstruct.optimizer as r_opt
+    import reconstruct.loss as r_loss
+    import reconstruct.loss_utils as r_lu
+    import reconstruct.utils as r_utils
+    import deep_sdf.deep_sdf_decoder as r_dec
+
+    ns = types.SimpleNamespace(optimizer=r_opt, loss=r_loss, loss_utils=r_lu, utils=r_utils,
+                               decoder=r_dec, torch=torch)
+    _loaded = ns
+    return ns
+
+
+def build_decoder(state_np):
+    """Instantiates the reference ``Decoder`` with the standard DeepSDF specs and loads ``state_np``
+    through a ``DataParallel`` wrapper exactly as ``deep_sdf/workspace.py:214-222`` does."""
+    ref = load()
+    torch = ref.torch
+    dec = ref.decoder.Decoder(64, dims=[512] * 8, dropout=list(range(8)), dropout_prob=0.2,
+                              norm_layers=list(range(8)), latent_in=[4], weight_norm=True,
+                              xyz_in_all=False, use_tanh=False, latent_dropout=False)
+    wrapped = torch.nn.DataParallel(dec)
+    sd = {"module." + k: torch.from_numpy(v.copy()) for k, v in state_np.items()}
+    wrapped.load_state_dict(sd)
+    dec = wrapped.module
+    dec.eval()
+    return dec
+
+
+def make_configs(cfg_dict):
+    ref = load()
+    return ref.utils.ForceKeyErrorDict(**cfg_dict)
