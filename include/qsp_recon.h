@@ -1,0 +1,124 @@
+/*
+ * qsp_recon.h - C ABI of the B200-native object reconstruction path.
+ *
+ * The reference (GetOverMassif/QSP-SLAM) has no C ABI for this path: its C++ core calls a Python
+ * class through pybind11::embed (src/LocalMapping.cc:42-69, src/LocalMapping_util.cc:139-140,
+ * :244-245, :705-706, :274).  This library sits UNDER a Python class with the same surface
+ * (qsp_slam_b200/reconstruct/optimizer.py) and each entry point below names the reference
+ * interface it replaces.  Plain C types only; pointers are host or device pointers as selected by
+ * QSP_FLAG_HOST_PTRS; every call is stream-ordered on `stream` (a cudaStream_t passed as void*,
+ * NULL = default stream); no exceptions cross the boundary; there is no global state besides the
+ * per-thread last-error string.  Return value: 0 on success, a negative qsp_status otherwise.
+ */
+#ifndef QSP_RECON_H
+#define QSP_RECON_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define QSP_CODE_LEN 64
+#define QSP_IN_DIM 67        /* [code(64), xyz(3)]  reconstruct/loss_utils.py:72,93 */
+#define QSP_JAC_STRIDE 68    /* rows of d sdf/d [code,xyz] are padded to 68 floats */
+#define QSP_RECORD_LEN 82    /* t_cam_obj (16, row-major) | code (64) | is_good | loss */
+#define QSP_POSE_DIM 7
+#define QSP_NDOF 71          /* 7 pose + 64 code unknowns (optimizer.py:212-217) */
+
+typedef enum qsp_status {
+  QSP_OK = 0,
+  QSP_ERR_INVALID = -1,      /* bad argument */
+  QSP_ERR_CUDA = -2,         /* a CUDA runtime call failed; see qsp_last_error() */
+  QSP_ERR_NO_DEVICE = -3,    /* no sm_100 device: there is NO CPU fallback */
+  QSP_ERR_ALLOC = -4
+} qsp_status;
+
+enum {
+  QSP_FLAG_HOST_PTRS = 1,    /* data pointers are host memory; the call copies h2d/d2h itself */
+  QSP_FLAG_SYNC = 2          /* cudaStreamSynchronize before returning */
+};
+
+/* Decoder parameters exactly as the deep_sdf state dict holds them
+ * (deep_sdf/deep_sdf_decoder.py:41-63): lin0..lin7 weight-normed, lin8 plain.
+ * weight_v[l]: (out_l, in_l) row-major; weight_g[l]: (out_l); bias[l]: (out_l).
+ * dims are fixed: in = {67,512,512,512,512,512,512,512,512}, out = {512,512,512,445,512,512,512,512,1}. */
+typedef struct qsp_decoder_weights {
+  const float* weight_v[8];
+  const float* weight_g[8];
+  const float* bias[8];
+  const float* lin8_weight;  /* (1,512) */
+  const float* lin8_bias;    /* (1) */
+} qsp_decoder_weights;
+
+/* Scalars Optimizer.__init__ copies from the JSON config (reconstruct/optimizer.py:27-44). */
+typedef struct qsp_gn_params {
+  float k1, k2, k3, k4;      /* render, sdf, code-regulariser, rotation-prior weights */
+  float b1, b2;              /* Huber thresholds: render, sdf */
+  float lr;                  /* learning_rate */
+  float s_damp;              /* scale_damping */
+  float cut_off;             /* cut_off_threshold th (sdf -> occupancy) */
+  int32_t num_iterations;    /* joint_optim.num_iterations */
+  int32_t num_depth_samples; /* S */
+  int32_t reserved;
+} qsp_gn_params;
+
+typedef struct qsp_decoder qsp_decoder; /* opaque: folded weights on one device + workspace */
+
+/* --- lifetime: replaces deep_sdf/workspace.py:202-224 config_decoder (weights -> device) ------ */
+int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_decoder** out);
+void qsp_decoder_destroy(qsp_decoder* dec);
+
+/* --- kernel (a), forward only: replaces reconstruct/loss_utils.py:51-79 decode_sdf ----------- */
+/* out[c*n + i] = sdf(codes[c], pts[i]);  codes (n_codes,64), pts (n,3), out (n_codes,n).       */
+int qsp_decode_sdf(qsp_decoder* dec, const float* codes, int32_t n_codes, const float* pts,
+                   int64_t n, float* out, uint32_t flags, void* stream);
+
+/* --- kernel (a), SDF + input Jacobian: replaces loss_utils.py:82-103 get_batch_sdf_jacobian -- */
+/* sdf (n), jac (n, QSP_JAC_STRIDE) = d sdf / d [code(64), xyz(3)], column 67 is zero.          */
+int qsp_decode_sdf_jacobian(qsp_decoder* dec, const float* code, const float* pts, int64_t n,
+                            float* sdf, float* jac, uint32_t flags, void* stream);
+
+/* --- the GN loop: replaces Optimizer.reconstruct_object (optimizer.py:96-281), batched -------- */
+/* B independent objects.  t_cam_obj (B,16) object->camera Sim(3) row-major; codes_in (B,64) or
+ * NULL (zero start code, optimizer.py:119-122); pts/rays are concatenated (sum,3) arrays with
+ * (B+1) int32 offsets; depth holds the foreground depths (K_b <= N_b per object), background rays
+ * follow the foreground rays of each object.  records (B, QSP_RECORD_LEN).  Offsets are always
+ * HOST pointers.  A failed object (optimizer.py:161-194) has is_good = 0 and its pose/code slots
+ * are NaN (the Python surface turns them into None).                                           */
+int qsp_reconstruct_batch(qsp_decoder* dec, const qsp_gn_params* prm, int32_t B,
+                          const float* t_cam_obj, const float* codes_in,
+                          const float* pts, const int32_t* pts_off,
+                          const float* rays, const int32_t* rays_off,
+                          const float* depth, const int32_t* depth_off,
+                          float* records, uint32_t flags, void* stream);
+
+/* --- pose-only GN: replaces Optimizer.estimate_pose_cam_obj (optimizer.py:47-93), batched ----- */
+/* t_co_se3 (B,16) SE(3), scale (B), codes (B,64); out (B,16) SE(3) object->camera.             */
+int qsp_estimate_pose_batch(qsp_decoder* dec, int32_t num_iterations, int32_t B,
+                            const float* t_co_se3, const float* scale, const float* codes,
+                            const float* pts, const int32_t* pts_off,
+                            float* out, uint32_t flags, void* stream);
+
+/* --- inspection of the last qsp_reconstruct_batch call (parity tests) -------------------------- */
+/* Per-iteration normal equations of object b: H (71,71), bvec (71), dx (71), counts (4) =
+ * {in-ball samples Q, band points, kept band points P, failed flag}.  Host pointers.  Only
+ * recorded when the handle is in debug mode (qsp_set_debug(dec,1)), which syncs per iteration. */
+int qsp_set_debug(qsp_decoder* dec, int32_t on);
+int qsp_get_iteration(qsp_decoder* dec, int32_t iteration, int32_t b, float* H, float* bvec,
+                      float* dx, int32_t* counts);
+/* kept band points of object b at `iteration`: ray index (within the object) and sample index,
+ * in the order the rows were accumulated; returns the count (<= cap) or a negative status.     */
+int qsp_get_band_indices(qsp_decoder* dec, int32_t iteration, int32_t b, int32_t* ray,
+                         int32_t* sample, int32_t cap);
+
+/* --- bookkeeping --------------------------------------------------------------------------------- */
+const char* qsp_last_error(void);
+int64_t qsp_launch_count(void);                 /* kernels launched by this library so far */
+int qsp_kernel_ms(qsp_decoder* dec, float* ms); /* device time of the last timed decoder launch */
+const char* qsp_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QSP_RECON_H */

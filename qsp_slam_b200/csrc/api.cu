@@ -1,0 +1,543 @@
+// C ABI of the reconstruction path (include/qsp_recon.h): handle, weight folding, workspace and the
+// per-iteration launch sequence.  Host code only orchestrates; all arithmetic is in the kernels.
+#include <atomic>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/qsp_recon.h"
+#include "decoder_ffma.cuh"
+#include "gn_kernels.cuh"
+
+static thread_local std::string g_err;
+static std::atomic<long long> g_launches{0};
+
+#define CK(call)                                                                          \
+  do {                                                                                    \
+    cudaError_t e_ = (call);                                                              \
+    if (e_ != cudaSuccess) {                                                              \
+      g_err = std::string(#call) + ": " + cudaGetErrorString(e_);                         \
+      return QSP_ERR_CUDA;                                                                \
+    }                                                                                     \
+  } while (0)
+#define LAUNCHED() (g_launches.fetch_add(1, std::memory_order_relaxed))
+
+struct Buf {
+  void* p = nullptr;
+  size_t bytes = 0;
+};
+
+struct IterDebug {
+  std::vector<float> H, b, dx;         // (B,71,71), (B,71), (B,71)
+  std::vector<int> counts;             // (B,4)
+  std::vector<int> band_off, row_ray, row_samp;
+};
+
+struct qsp_decoder {
+  int device = 0;
+  int num_sms = 148;
+  DecoderDev dw{};
+  std::vector<void*> weight_allocs;
+  // workspace (grown on demand, owned by the handle)
+  Buf in_T, in_code, in_pts, in_rays, in_depth, in_scale, out_rec;
+  Buf pts_off, rays_off, depth_off, ray_obj, pt_obj;
+  Buf state, counters, ray_cnt, ray_base, band_cnt, band_base;
+  Buf q_pts, q_code, q_sdf, slot, ray_res;
+  Buf jp_pts, jp_code, g_sdf, g_jac, row_fac, row_res, row_ray, row_samp, row_active, m_active;
+  Buf partials, dbgH, dbgb, dbgdx;
+  Buf dec_pts, dec_codes, dec_out, dec_jac;
+  bool debug = false;
+  std::vector<IterDebug> dbg;
+  std::vector<int> h_rays_off;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  float last_ms = 0.f;
+};
+
+template <typename T>
+static int ensure(Buf& b, size_t n, T** out) {
+  size_t need = n * sizeof(T);
+  if (need == 0) need = sizeof(T);
+  if (b.bytes < need) {
+    if (b.p) cudaFree(b.p);
+    b.p = nullptr;
+    b.bytes = 0;
+    size_t cap = need + need / 4 + 256;
+    if (cudaMalloc(&b.p, cap) != cudaSuccess) {
+      g_err = "cudaMalloc failed";
+      return QSP_ERR_ALLOC;
+    }
+    b.bytes = cap;
+  }
+  *out = reinterpret_cast<T*>(b.p);
+  return QSP_OK;
+}
+#define ENSURE(buf, n, ptr)                       \
+  do {                                            \
+    int r_ = ensure(buf, (size_t)(n), &(ptr));    \
+    if (r_ != QSP_OK) return r_;                  \
+  } while (0)
+
+extern "C" const char* qsp_last_error(void) { return g_err.c_str(); }
+extern "C" int64_t qsp_launch_count(void) { return (int64_t)g_launches.load(); }
+extern "C" const char* qsp_version(void) { return "qsp_recon 0.1 (sm_100a)"; }
+
+// ------------------------------------------------------------------------------------------------
+// weights: fold weight norm (W = g * v / ||v||_row, torch weight_norm dim=0) and lay the operands
+// out for the kernels
+// ------------------------------------------------------------------------------------------------
+static const int kIn[9] = {67, 512, 512, 512, 512, 512, 512, 512, 512};
+static const int kOut[9] = {512, 512, 512, 445, 512, 512, 512, 512, 1};
+
+static int upload(qsp_decoder* d, const std::vector<float>& h, const float** dev) {
+  void* p = nullptr;
+  CK(cudaMalloc(&p, h.size() * sizeof(float)));
+  d->weight_allocs.push_back(p);
+  CK(cudaMemcpy(p, h.data(), h.size() * sizeof(float), cudaMemcpyHostToDevice));
+  *dev = reinterpret_cast<const float*>(p);
+  return QSP_OK;
+}
+
+extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_decoder** out) {
+  if (!w || !out) { g_err = "null argument"; return QSP_ERR_INVALID; }
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= device) {
+    g_err = "no CUDA device: this library has no CPU fallback";
+    return QSP_ERR_NO_DEVICE;
+  }
+  CK(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CK(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) {
+    g_err = "device is not sm_100: this library is built for B200 only";
+    return QSP_ERR_NO_DEVICE;
+  }
+  qsp_decoder* d = new qsp_decoder();
+  d->device = device;
+  d->num_sms = prop.multiProcessorCount;
+  for (int l = 0; l < 8; ++l) {
+    const int in = kIn[l], on = kOut[l];
+    const int kpad = l == 0 ? 80 : 512;
+    std::vector<float> W((size_t)on * in), Wf((size_t)kpad * 512, 0.f), Wb((size_t)512 * 512, 0.f), bias(512, 0.f);
+    for (int o = 0; o < on; ++o) {
+      const float* v = w->weight_v[l] + (size_t)o * in;
+      double nn = 0;
+      for (int i = 0; i < in; ++i) nn += (double)v[i] * v[i];
+      float scale = w->weight_g[l][o] / (float)std::sqrt(nn);
+      for (int i = 0; i < in; ++i) W[(size_t)o * in + i] = v[i] * scale;
+      bias[o] = w->bias[l][o];
+    }
+    for (int o = 0; o < on; ++o)
+      for (int i = 0; i < in; ++i) {
+        Wf[(size_t)i * 512 + o] = W[(size_t)o * in + i];
+        Wb[(size_t)o * 512 + i] = W[(size_t)o * in + i];
+      }
+    int r;
+    if ((r = upload(d, Wf, &d->dw.Wf[l])) || (r = upload(d, Wb, &d->dw.Wb[l])) || (r = upload(d, bias, &d->dw.bias[l]))) {
+      qsp_decoder_destroy(d);
+      return r;
+    }
+    d->dw.kf[l] = kpad;
+  }
+  std::vector<float> w8(w->lin8_weight, w->lin8_weight + 512);
+  int r = upload(d, w8, &d->dw.w8);
+  if (r) { qsp_decoder_destroy(d); return r; }
+  d->dw.b8 = w->lin8_bias[0];
+  CK(cudaFuncSetAttribute(k_decoder_ffma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FF_SMEM_BYTES));
+  CK(cudaFuncSetAttribute(k_decoder_ffma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FF_SMEM_BYTES));
+  CK(cudaEventCreate(&d->ev0));
+  CK(cudaEventCreate(&d->ev1));
+  *out = d;
+  return QSP_OK;
+}
+
+extern "C" void qsp_decoder_destroy(qsp_decoder* d) {
+  if (!d) return;
+  cudaSetDevice(d->device);
+  for (void* p : d->weight_allocs) cudaFree(p);
+  Buf* bufs[] = {&d->in_T, &d->in_code, &d->in_pts, &d->in_rays, &d->in_depth, &d->in_scale, &d->out_rec,
+                 &d->pts_off, &d->rays_off, &d->depth_off, &d->ray_obj, &d->pt_obj, &d->state, &d->counters,
+                 &d->ray_cnt, &d->ray_base, &d->band_cnt, &d->band_base, &d->q_pts, &d->q_code, &d->q_sdf,
+                 &d->slot, &d->ray_res, &d->jp_pts, &d->jp_code, &d->g_sdf, &d->g_jac, &d->row_fac,
+                 &d->row_res, &d->row_ray, &d->row_samp, &d->row_active, &d->m_active, &d->partials,
+                 &d->dbgH, &d->dbgb, &d->dbgdx, &d->dec_pts, &d->dec_codes, &d->dec_out, &d->dec_jac};
+  for (Buf* b : bufs)
+    if (b->p) cudaFree(b->p);
+  if (d->ev0) cudaEventDestroy(d->ev0);
+  if (d->ev1) cudaEventDestroy(d->ev1);
+  delete d;
+}
+
+extern "C" int qsp_kernel_ms(qsp_decoder* d, float* ms) {
+  if (!d || !ms) return QSP_ERR_INVALID;
+  *ms = d->last_ms;
+  return QSP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// kernel (a) entry points
+// ------------------------------------------------------------------------------------------------
+static int launch_decoder(qsp_decoder* d, bool jac, const float* pts, const int* code_idx, const float* codes,
+                          int code_stride, long n, const int* n_dev, int n_codes_y, float* sdf, float* jacp,
+                          cudaStream_t st) {
+  long tiles = n_dev ? (long)d->num_sms : ((n + FF_TILE - 1) / FF_TILE) * n_codes_y;
+  if (tiles <= 0) return QSP_OK;
+  dim3 grid((unsigned)std::min<long>(tiles, d->num_sms));   // persistent: one CTA per SM
+  if (jac)
+    k_decoder_ffma<true><<<grid, FF_THREADS, FF_SMEM_BYTES, st>>>(d->dw, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
+  else
+    k_decoder_ffma<false><<<grid, FF_THREADS, FF_SMEM_BYTES, st>>>(d->dw, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
+  LAUNCHED();
+  CK(cudaGetLastError());
+  return QSP_OK;
+}
+
+extern "C" int qsp_decode_sdf(qsp_decoder* d, const float* codes, int32_t n_codes, const float* pts,
+                              int64_t n, float* out, uint32_t flags, void* stream) {
+  if (!d || !codes || !pts || !out || n_codes <= 0 || n < 0) { g_err = "bad argument"; return QSP_ERR_INVALID; }
+  CK(cudaSetDevice(d->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const float *dc = codes, *dp = pts;
+  float* dout = out;
+  if (flags & QSP_FLAG_HOST_PTRS) {
+    float *c, *p;
+    ENSURE(d->dec_codes, (size_t)n_codes * 64, c);
+    ENSURE(d->dec_pts, (size_t)n * 3, p);
+    ENSURE(d->dec_out, (size_t)n_codes * n, dout);
+    CK(cudaMemcpyAsync(c, codes, (size_t)n_codes * 64 * 4, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(p, pts, (size_t)n * 3 * 4, cudaMemcpyHostToDevice, st));
+    dc = c; dp = p;
+  }
+  CK(cudaEventRecord(d->ev0, st));
+  // grid.y is limited to 65535 codes per launch; the callers stay far below that
+  int r = launch_decoder(d, false, dp, nullptr, dc, 64, n, nullptr, n_codes, dout, nullptr, st);
+  if (r) return r;
+  CK(cudaEventRecord(d->ev1, st));
+  if (flags & QSP_FLAG_HOST_PTRS) {
+    CK(cudaMemcpyAsync(out, dout, (size_t)n_codes * n * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+  } else if (flags & QSP_FLAG_SYNC) {
+    CK(cudaStreamSynchronize(st));
+  }
+  if (flags & (QSP_FLAG_HOST_PTRS | QSP_FLAG_SYNC)) CK(cudaEventElapsedTime(&d->last_ms, d->ev0, d->ev1));
+  return QSP_OK;
+}
+
+extern "C" int qsp_decode_sdf_jacobian(qsp_decoder* d, const float* code, const float* pts, int64_t n,
+                                       float* sdf, float* jac, uint32_t flags, void* stream) {
+  if (!d || !code || !pts || !sdf || !jac || n < 0) { g_err = "bad argument"; return QSP_ERR_INVALID; }
+  CK(cudaSetDevice(d->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const float *dc = code, *dp = pts;
+  float *ds = sdf, *dj = jac;
+  if (flags & QSP_FLAG_HOST_PTRS) {
+    float *c, *p;
+    ENSURE(d->dec_codes, 64, c);
+    ENSURE(d->dec_pts, (size_t)n * 3, p);
+    ENSURE(d->dec_out, (size_t)n, ds);
+    ENSURE(d->dec_jac, (size_t)n * QSP_JSTRIDE, dj);
+    CK(cudaMemcpyAsync(c, code, 64 * 4, cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(p, pts, (size_t)n * 3 * 4, cudaMemcpyHostToDevice, st));
+    dc = c; dp = p;
+  }
+  CK(cudaEventRecord(d->ev0, st));
+  int r = launch_decoder(d, true, dp, nullptr, dc, 64, n, nullptr, 1, ds, dj, st);
+  if (r) return r;
+  CK(cudaEventRecord(d->ev1, st));
+  if (flags & QSP_FLAG_HOST_PTRS) {
+    CK(cudaMemcpyAsync(sdf, ds, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(jac, dj, (size_t)n * QSP_JSTRIDE * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+  } else if (flags & QSP_FLAG_SYNC) {
+    CK(cudaStreamSynchronize(st));
+  }
+  if (flags & (QSP_FLAG_HOST_PTRS | QSP_FLAG_SYNC)) CK(cudaEventElapsedTime(&d->last_ms, d->ev0, d->ev1));
+  return QSP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// the Gauss-Newton loop
+// ------------------------------------------------------------------------------------------------
+__global__ void k_fill_obj_map(const int* __restrict__ off, int B, int* __restrict__ map) {
+  int o = blockIdx.x;
+  for (int i = off[o] + threadIdx.x; i < off[o + 1]; i += blockDim.x) map[i] = o;
+}
+__global__ void k_fill_float(float* p, int n, float v) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+__global__ void k_count_active(const int* __restrict__ pts_off, int B, int* __restrict__ m_active) {
+  int o = blockIdx.x * blockDim.x + threadIdx.x;
+  if (o < B) m_active[o] = pts_off[o + 1] - pts_off[o];
+}
+
+struct Inputs {
+  const float *T, *codes, *pts, *rays, *depth, *scale;
+};
+
+static int stage(qsp_decoder* d, Buf& b, const float* src, size_t n, bool host, cudaStream_t st, const float** out) {
+  if (!src) { *out = nullptr; return QSP_OK; }
+  if (!host) { *out = src; return QSP_OK; }
+  float* p;
+  ENSURE(b, n, p);
+  CK(cudaMemcpyAsync(p, src, n * sizeof(float), cudaMemcpyHostToDevice, st));
+  *out = p;
+  return QSP_OK;
+}
+static int stage_off(Buf& b, const int32_t* src, int B, cudaStream_t st, int** out) {
+  int* p;
+  ENSURE(b, (size_t)B + 1, p);
+  CK(cudaMemcpyAsync(p, src, ((size_t)B + 1) * sizeof(int), cudaMemcpyHostToDevice, st));
+  *out = p;
+  return QSP_OK;
+}
+
+static int check_offsets(const int32_t* off, int B, const char* name) {
+  if (!off || off[0] != 0) { g_err = std::string(name) + " offsets must start at 0"; return QSP_ERR_INVALID; }
+  for (int i = 0; i < B; ++i)
+    if (off[i + 1] < off[i]) { g_err = std::string(name) + " offsets must be non-decreasing"; return QSP_ERR_INVALID; }
+  return QSP_OK;
+}
+
+extern "C" int qsp_set_debug(qsp_decoder* d, int32_t on) {
+  if (!d) return QSP_ERR_INVALID;
+  d->debug = on != 0;
+  d->dbg.clear();
+  return QSP_OK;
+}
+
+extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, int32_t B,
+                                     const float* t_cam_obj, const float* codes_in,
+                                     const float* pts, const int32_t* pts_off,
+                                     const float* rays, const int32_t* rays_off,
+                                     const float* depth, const int32_t* depth_off,
+                                     float* records, uint32_t flags, void* stream) {
+  if (!d || !prm || B <= 0 || !t_cam_obj || !pts || !rays || !depth || !records) {
+    g_err = "bad argument";
+    return QSP_ERR_INVALID;
+  }
+  int r;
+  if ((r = check_offsets(pts_off, B, "pts")) || (r = check_offsets(rays_off, B, "rays")) ||
+      (r = check_offsets(depth_off, B, "depth"))) return r;
+  const int S = prm->num_depth_samples;
+  if (S < 2 || S > 32 * GN_MAXC) { g_err = "num_depth_samples must be in [2, 256]"; return QSP_ERR_INVALID; }
+  for (int i = 0; i < B; ++i)
+    if (depth_off[i + 1] - depth_off[i] > rays_off[i + 1] - rays_off[i]) {
+      g_err = "more depth values than rays";
+      return QSP_ERR_INVALID;
+    }
+  CK(cudaSetDevice(d->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool host = flags & QSP_FLAG_HOST_PTRS;
+  const int M = pts_off[B], R = rays_off[B], K = depth_off[B];
+  const size_t qcap = (size_t)R * S;
+  const size_t bandcap = qcap / 4 + 4096;
+  const size_t rowcap = (size_t)M + bandcap;
+
+  Inputs in{};
+  if ((r = stage(d, d->in_T, t_cam_obj, (size_t)B * 16, host, st, &in.T)) ||
+      (r = stage(d, d->in_code, codes_in, (size_t)B * 64, host, st, &in.codes)) ||
+      (r = stage(d, d->in_pts, pts, (size_t)M * 3, host, st, &in.pts)) ||
+      (r = stage(d, d->in_rays, rays, (size_t)R * 3, host, st, &in.rays)) ||
+      (r = stage(d, d->in_depth, depth, (size_t)std::max(K, 1), host && K > 0, st, &in.depth))) return r;
+  int *d_pts_off, *d_rays_off, *d_depth_off;
+  if ((r = stage_off(d->pts_off, pts_off, B, st, &d_pts_off)) || (r = stage_off(d->rays_off, rays_off, B, st, &d_rays_off)) ||
+      (r = stage_off(d->depth_off, depth_off, B, st, &d_depth_off))) return r;
+
+  ObjState* state; int *counters, *ray_obj, *pt_obj, *ray_cnt, *ray_base, *band_cnt, *band_base;
+  float *q_pts, *q_sdf, *slot, *ray_res, *jp_pts, *g_sdf, *g_jac, *row_fac, *row_res, *partials, *d_rec;
+  int *q_code, *jp_code, *row_ray, *row_samp;
+  ENSURE(d->state, B, state);
+  ENSURE(d->counters, 8, counters);
+  ENSURE(d->ray_obj, R, ray_obj);
+  ENSURE(d->pt_obj, M, pt_obj);
+  ENSURE(d->ray_cnt, R, ray_cnt);
+  ENSURE(d->ray_base, R + 1, ray_base);
+  ENSURE(d->band_cnt, R, band_cnt);
+  ENSURE(d->band_base, R + 1, band_base);
+  ENSURE(d->q_pts, qcap * 3, q_pts);
+  ENSURE(d->q_code, qcap, q_code);
+  ENSURE(d->q_sdf, qcap, q_sdf);
+  ENSURE(d->slot, qcap, slot);
+  ENSURE(d->ray_res, R, ray_res);
+  ENSURE(d->jp_pts, rowcap * 3, jp_pts);
+  ENSURE(d->jp_code, rowcap, jp_code);
+  ENSURE(d->g_sdf, rowcap, g_sdf);
+  ENSURE(d->g_jac, rowcap * QSP_JSTRIDE, g_jac);
+  ENSURE(d->row_fac, rowcap, row_fac);
+  ENSURE(d->row_res, rowcap, row_res);
+  ENSURE(d->row_ray, rowcap, row_ray);
+  ENSURE(d->row_samp, rowcap, row_samp);
+  const int nchunk = std::max(1, std::min(16, 2 * d->num_sms / B));
+  ENSURE(d->partials, (size_t)B * 2 * nchunk * QSP_PART_STRIDE, partials);
+  d_rec = records;
+  if (host) ENSURE(d->out_rec, (size_t)B * QSP_RECORD_LEN, d_rec);
+  float *dbgH = nullptr, *dbgb = nullptr, *dbgdx = nullptr;
+  if (d->debug) {
+    ENSURE(d->dbgH, (size_t)B * 71 * 71, dbgH);
+    ENSURE(d->dbgb, (size_t)B * 71, dbgb);
+    ENSURE(d->dbgdx, (size_t)B * 71, dbgdx);
+    d->dbg.clear();
+    d->h_rays_off.assign(rays_off, rays_off + B + 1);
+  }
+
+  GnParamsDev p{prm->k1, prm->k2, prm->k3, prm->k4, prm->b1, prm->b2, prm->lr, prm->s_damp, prm->cut_off,
+                prm->num_iterations, S};
+  const int tb = 256;
+  k_fill_obj_map<<<B, 128, 0, st>>>(d_rays_off, B, ray_obj); LAUNCHED();
+  k_fill_obj_map<<<B, 128, 0, st>>>(d_pts_off, B, pt_obj); LAUNCHED();
+  k_init_state<<<(B + 63) / 64, 64, 0, st>>>(state, in.T, in.codes, B); LAUNCHED();
+  const int ray_blocks = (R * 32 + tb - 1) / tb;
+  const float* codes_dev = reinterpret_cast<const float*>(state) + offsetof(ObjState, code) / 4;
+  const int code_stride = sizeof(ObjState) / 4;
+
+  for (int it = 0; it < prm->num_iterations; ++it) {
+    k_prep<<<(B + 63) / 64, 64, 0, st>>>(state, B, S); LAUNCHED();
+    // (b) sample, in-ball test, ordered compaction
+    k_sample<false><<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, R, S, ray_cnt, nullptr, nullptr, nullptr); LAUNCHED();
+    k_exclusive_scan<<<1, 1024, 0, st>>>(ray_cnt, ray_base, R, counters + 0, 0, nullptr); LAUNCHED();
+    k_sample<true><<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, R, S, nullptr, ray_base, q_pts, q_code); LAUNCHED();
+    // (a) forward decode of the in-ball samples (loss.py:77-78)
+    if ((r = launch_decoder(d, false, q_pts, q_code, codes_dev, code_stride, 0, counters + 0, 1, q_sdf, nullptr, st))) return r;
+    // (b) occupancy, transmittance, rendered depth, band selection
+    k_render<<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, d_rays_off, in.depth, d_depth_off, R, S, p.th,
+                                        ray_base, q_sdf, slot, ray_res, band_cnt); LAUNCHED();
+    k_exclusive_scan<<<1, 1024, 0, st>>>(band_cnt, band_base, R, counters + 1, M, counters + 2); LAUNCHED();
+    k_band_fill<<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, R, S, slot, ray_res, band_base, M, jp_pts, jp_code,
+                                           row_fac, row_res, row_ray, row_samp); LAUNCHED();
+    k_surface_xform<<<(M + tb - 1) / tb, tb, 0, st>>>(state, in.pts, pt_obj, M, jp_pts, jp_code); LAUNCHED();
+    // (a) SDF + input Jacobian of surface and band points (loss.py:34,144)
+    if ((r = launch_decoder(d, true, jp_pts, jp_code, codes_dev, code_stride, 0, counters + 2, 1, g_sdf, g_jac, st))) return r;
+    // (c) chain rule + normal equations, (d) solve + update
+    k_accumulate<<<dim3(nchunk, B, 2), 256, 0, st>>>(state, d_pts_off, d_rays_off, band_base, M, jp_pts, g_sdf, g_jac,
+                                                     row_fac, row_res, p.b2, p.b1, 0, nullptr, partials); LAUNCHED();
+    k_solve<<<B, 128, 0, st>>>(state, d_pts_off, nchunk, partials, p, 0, nullptr, dbgH, dbgb, dbgdx); LAUNCHED();
+    CK(cudaGetLastError());
+    if (d->debug) {  // parity inspection: copy this iteration's normal equations and index lists out
+      CK(cudaStreamSynchronize(st));
+      IterDebug g;
+      g.H.resize((size_t)B * 71 * 71); g.b.resize((size_t)B * 71); g.dx.resize((size_t)B * 71);
+      g.counts.resize((size_t)B * 4); g.band_off.resize(R + 1);
+      CK(cudaMemcpy(g.H.data(), dbgH, g.H.size() * 4, cudaMemcpyDeviceToHost));
+      CK(cudaMemcpy(g.b.data(), dbgb, g.b.size() * 4, cudaMemcpyDeviceToHost));
+      CK(cudaMemcpy(g.dx.data(), dbgdx, g.dx.size() * 4, cudaMemcpyDeviceToHost));
+      CK(cudaMemcpy(g.band_off.data(), band_base, (size_t)(R + 1) * 4, cudaMemcpyDeviceToHost));
+      std::vector<ObjState> hs(B);
+      CK(cudaMemcpy(hs.data(), state, (size_t)B * sizeof(ObjState), cudaMemcpyDeviceToHost));
+      for (int o = 0; o < B; ++o) {
+        g.counts[o * 4 + 0] = hs[o].n_inball; g.counts[o * 4 + 1] = hs[o].n_band;
+        g.counts[o * 4 + 2] = hs[o].n_keep; g.counts[o * 4 + 3] = hs[o].failed;
+      }
+      int P = std::min<int>(g.band_off[R], (int)bandcap);
+      g.row_ray.resize(P); g.row_samp.resize(P);
+      if (P > 0) {
+        CK(cudaMemcpy(g.row_ray.data(), row_ray + M, (size_t)P * 4, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(g.row_samp.data(), row_samp + M, (size_t)P * 4, cudaMemcpyDeviceToHost));
+      }
+      d->dbg.push_back(std::move(g));
+    }
+  }
+  k_finalize<<<(B + 63) / 64, 64, 0, st>>>(state, B, d_rec); LAUNCHED();
+  CK(cudaGetLastError());
+  if (host) {
+    CK(cudaMemcpyAsync(records, d_rec, (size_t)B * QSP_RECORD_LEN * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+  } else if (flags & QSP_FLAG_SYNC) {
+    CK(cudaStreamSynchronize(st));
+  }
+  return QSP_OK;
+}
+
+extern "C" int qsp_get_iteration(qsp_decoder* d, int32_t it, int32_t b, float* H, float* bvec, float* dx,
+                                 int32_t* counts) {
+  if (!d || it < 0 || it >= (int)d->dbg.size()) { g_err = "no such recorded iteration"; return QSP_ERR_INVALID; }
+  const IterDebug& g = d->dbg[it];
+  if (b < 0 || (size_t)b * 71 >= g.b.size()) { g_err = "no such object"; return QSP_ERR_INVALID; }
+  if (H) memcpy(H, g.H.data() + (size_t)b * 71 * 71, 71 * 71 * 4);
+  if (bvec) memcpy(bvec, g.b.data() + (size_t)b * 71, 71 * 4);
+  if (dx) memcpy(dx, g.dx.data() + (size_t)b * 71, 71 * 4);
+  if (counts) memcpy(counts, g.counts.data() + (size_t)b * 4, 4 * 4);
+  return QSP_OK;
+}
+
+extern "C" int qsp_get_band_indices(qsp_decoder* d, int32_t it, int32_t b, int32_t* ray, int32_t* sample,
+                                    int32_t cap) {
+  if (!d || it < 0 || it >= (int)d->dbg.size()) { g_err = "no such recorded iteration"; return QSP_ERR_INVALID; }
+  const IterDebug& g = d->dbg[it];
+  if (b < 0 || b + 1 >= (int)d->h_rays_off.size()) { g_err = "no such object"; return QSP_ERR_INVALID; }
+  int r0 = d->h_rays_off[b], r1 = d->h_rays_off[b + 1];
+  int lo = g.band_off[r0], hi = std::min<int>(g.band_off[r1], (int)g.row_ray.size());
+  int n = std::max(0, hi - lo);
+  for (int i = 0; i < n && i < cap; ++i) {
+    if (ray) ray[i] = g.row_ray[lo + i] - r0;
+    if (sample) sample[i] = g.row_samp[lo + i];
+  }
+  return n;
+}
+
+// ------------------------------------------------------------------------------------------------
+// pose-only GN (optimizer.py:47-93)
+// ------------------------------------------------------------------------------------------------
+extern "C" int qsp_estimate_pose_batch(qsp_decoder* d, int32_t num_iterations, int32_t B,
+                                       const float* t_co_se3, const float* scale, const float* codes,
+                                       const float* pts, const int32_t* pts_off, float* out,
+                                       uint32_t flags, void* stream) {
+  if (!d || B <= 0 || !t_co_se3 || !scale || !codes || !pts || !out || num_iterations < 0) {
+    g_err = "bad argument";
+    return QSP_ERR_INVALID;
+  }
+  int r;
+  if ((r = check_offsets(pts_off, B, "pts"))) return r;
+  CK(cudaSetDevice(d->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const bool host = flags & QSP_FLAG_HOST_PTRS;
+  const int M = pts_off[B];
+  Inputs in{};
+  if ((r = stage(d, d->in_T, t_co_se3, (size_t)B * 16, host, st, &in.T)) ||
+      (r = stage(d, d->in_scale, scale, (size_t)B, host, st, &in.scale)) ||
+      (r = stage(d, d->in_code, codes, (size_t)B * 64, host, st, &in.codes)) ||
+      (r = stage(d, d->in_pts, pts, (size_t)M * 3, host, st, &in.pts))) return r;
+  int *d_pts_off, *pt_obj, *jp_code, *m_active;
+  if ((r = stage_off(d->pts_off, pts_off, B, st, &d_pts_off))) return r;
+  ObjState* state;
+  float *jp_pts, *g_sdf, *g_jac, *partials, *row_active, *d_out = out;
+  ENSURE(d->state, B, state);
+  ENSURE(d->pt_obj, M, pt_obj);
+  ENSURE(d->jp_pts, (size_t)M * 3, jp_pts);
+  ENSURE(d->jp_code, M, jp_code);
+  ENSURE(d->g_sdf, M, g_sdf);
+  ENSURE(d->g_jac, (size_t)M * QSP_JSTRIDE, g_jac);
+  ENSURE(d->row_active, M, row_active);
+  ENSURE(d->m_active, B, m_active);
+  const int nchunk = std::max(1, std::min(16, 2 * d->num_sms / B));
+  ENSURE(d->partials, (size_t)B * 2 * nchunk * QSP_PART_STRIDE, partials);
+  if (host) ENSURE(d->out_rec, (size_t)B * 16, d_out);
+  const int tb = 256;
+  GnParamsDev p{};
+  k_fill_obj_map<<<B, 128, 0, st>>>(d_pts_off, B, pt_obj); LAUNCHED();
+  k_init_pose_only<<<(B + 63) / 64, 64, 0, st>>>(state, in.T, in.scale, in.codes, B); LAUNCHED();
+  k_fill_float<<<(M + tb - 1) / tb, tb, 0, st>>>(row_active, M, 1.f); LAUNCHED();
+  k_count_active<<<(B + 63) / 64, 64, 0, st>>>(d_pts_off, B, m_active); LAUNCHED();
+  const float* codes_dev = reinterpret_cast<const float*>(state) + offsetof(ObjState, code) / 4;
+  for (int it = 0; it < num_iterations; ++it) {
+    k_surface_xform<<<(M + tb - 1) / tb, tb, 0, st>>>(state, in.pts, pt_obj, M, jp_pts, jp_code); LAUNCHED();
+    if ((r = launch_decoder(d, true, jp_pts, jp_code, codes_dev, sizeof(ObjState) / 4, M, nullptr, 1, g_sdf, g_jac, st))) return r;
+    k_accumulate<<<dim3(nchunk, B, 1), 256, 0, st>>>(state, d_pts_off, d_pts_off, nullptr, M, jp_pts, g_sdf, g_jac,
+                                                     nullptr, nullptr, 0.f, 0.f, 1, row_active, partials); LAUNCHED();
+    k_solve<<<B, 128, 0, st>>>(state, d_pts_off, nchunk, partials, p, 1, m_active, nullptr, nullptr, nullptr); LAUNCHED();
+    if (it == 4) {  // optimizer.py:80-82
+      CK(cudaMemsetAsync(m_active, 0, (size_t)B * 4, st));
+      k_prune<<<(M + tb - 1) / tb, tb, 0, st>>>(g_sdf, pt_obj, M, row_active, m_active); LAUNCHED();
+    }
+  }
+  k_finalize_pose_only<<<(B + 63) / 64, 64, 0, st>>>(state, in.scale, B, d_out); LAUNCHED();
+  CK(cudaGetLastError());
+  if (host) {
+    CK(cudaMemcpyAsync(out, d_out, (size_t)B * 16 * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+  } else if (flags & QSP_FLAG_SYNC) {
+    CK(cudaStreamSynchronize(st));
+  }
+  return QSP_OK;
+}

@@ -1,0 +1,637 @@
+// Kernels (b), (c), (d) of the Gauss-Newton loop and the per-iteration bookkeeping.
+// Everything is driven by device-side counts, so one iteration is a fixed launch sequence with no
+// host synchronisation.  Reference: reconstruct/optimizer.py:141-263, reconstruct/loss.py.
+#pragma once
+#include "common.cuh"
+
+#define GN_MAXC 8                 // depth samples per ray <= 32 * GN_MAXC
+#define GN_SLOT 32                // rows staged per accumulation step
+
+// ------------------------------------------------------------------------------------------------
+// small dense helpers (per-thread, fp64 internally so that they are at least as accurate as the
+// LAPACK fp32 routines the reference calls: torch.inverse / torch.det)
+// ------------------------------------------------------------------------------------------------
+__device__ inline void inv3_d(const double a[9], double o[9], double* det) {
+  double c0 = a[4] * a[8] - a[5] * a[7], c1 = a[5] * a[6] - a[3] * a[8], c2 = a[3] * a[7] - a[4] * a[6];
+  double d = a[0] * c0 + a[1] * c1 + a[2] * c2;
+  double id = 1.0 / d;
+  o[0] = c0 * id; o[1] = (a[2] * a[7] - a[1] * a[8]) * id; o[2] = (a[1] * a[5] - a[2] * a[4]) * id;
+  o[3] = c1 * id; o[4] = (a[0] * a[8] - a[2] * a[6]) * id; o[5] = (a[2] * a[3] - a[0] * a[5]) * id;
+  o[6] = c2 * id; o[7] = (a[1] * a[6] - a[0] * a[7]) * id; o[8] = (a[0] * a[4] - a[1] * a[3]) * id;
+  *det = d;
+}
+
+// inverse of an affine 4x4 [A t; 0 1] (row-major floats): [A^-1, -A^-1 t]
+__device__ inline float inv_affine(const float* T, float* O) {
+  double a[9], ai[9], det;
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 3; ++c) a[r * 3 + c] = T[r * 4 + c];
+  inv3_d(a, ai, &det);
+  for (int r = 0; r < 3; ++r) {
+    double tr = 0;
+    for (int c = 0; c < 3; ++c) {
+      O[r * 4 + c] = (float)ai[r * 3 + c];
+      tr += ai[r * 3 + c] * (double)T[c * 4 + 3];
+    }
+    O[r * 4 + 3] = (float)(-tr);
+  }
+  O[12] = O[13] = O[14] = 0.f;
+  O[15] = 1.f;
+  return (float)det;
+}
+
+// sample depth j of torch.linspace(d_min, d_max, S) (symmetric evaluation, ATen RangeFactories)
+__device__ __forceinline__ float linspace_at(float d_min, float d_max, float step, int j, int S) {
+  return j < S / 2 ? __fadd_rn(d_min, __fmul_rn(step, (float)j))
+                   : __fsub_rn(d_max, __fmul_rn(step, (float)(S - 1 - j)));
+}
+
+// x_o = R (ray * d) + t with the reference's operation order (loss.py:60-63), no FMA contraction
+__device__ __forceinline__ void sample_point(const float* __restrict__ T, float rx, float ry, float rz,
+                                             float d, float& x, float& y, float& z) {
+  float cx = __fmul_rn(rx, d), cy = __fmul_rn(ry, d), cz = __fmul_rn(rz, d);
+  x = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(cx, T[0]), __fmul_rn(cy, T[1])), __fmul_rn(cz, T[2])), T[3]);
+  y = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(cx, T[4]), __fmul_rn(cy, T[5])), __fmul_rn(cz, T[6])), T[7]);
+  z = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(cx, T[8]), __fmul_rn(cy, T[9])), __fmul_rn(cz, T[10])), T[11]);
+}
+__device__ __forceinline__ bool in_ball(float x, float y, float z) {
+  return sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)), __fmul_rn(z, z))) < 1.0f;  // loss.py:68
+}
+
+// ------------------------------------------------------------------------------------------------
+// state set-up
+// ------------------------------------------------------------------------------------------------
+__global__ void k_init_state(ObjState* st, const float* __restrict__ t_cam_obj,
+                             const float* __restrict__ codes_in, int B) {
+  int o = blockIdx.x * blockDim.x + threadIdx.x;
+  if (o >= B) return;
+  ObjState& s = st[o];
+  inv_affine(t_cam_obj + o * 16, s.T_oc);            // optimizer.py:125-126
+  for (int c = 0; c < 64; ++c) s.code[c] = codes_in ? codes_in[o * 64 + c] : 0.f;  // :119-122
+  s.loss = 0.f;
+  s.failed = 0;
+  s.n_inball = s.n_band = s.n_keep = 0;
+}
+
+// depth range, background depth and rotation prior of the current pose (optimizer.py:144-153,
+// loss.py:155-178)
+__global__ void k_prep(ObjState* st, int B, int S) {
+  int o = blockIdx.x * blockDim.x + threadIdx.x;
+  if (o >= B) return;
+  ObjState& s = st[o];
+  if (s.failed) return;
+  float det = inv_affine(s.T_oc, s.T_co);
+  float scale = cbrtf(det);
+  s.scale = scale;
+  s.d_min = __fsub_rn(s.T_co[11], scale);
+  s.d_max = __fadd_rn(s.T_co[11], scale);
+  s.delta_d = __fdiv_rn(__fsub_rn(s.d_max, s.d_min), (float)(S - 1));
+  s.n_inball = s.n_band = s.n_keep = 0;
+  // rotation prior: res = 1 - (R_co e_y).n_g = 1 + R_co[1][1]
+  double rc[9], ro[9], dd;
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 3; ++c) rc[r * 3 + c] = (double)__fdiv_rn(s.T_co[r * 4 + c], scale);
+  float res = __fadd_rn(1.0f, (float)rc[4]);
+  if (res < 1e-7f) {
+    s.J_rot[0] = s.J_rot[1] = s.J_rot[2] = 0.f;
+    s.res_rot = 0.f;
+  } else {
+    inv3_d(rc, ro, &dd);                              // R_oc
+    // (R_oc n_g) x e_y with n_g = (0,-1,0): v = -R_oc[:,1]; v x e_y = (-v_z, 0, v_x)
+    s.J_rot[0] = (float)ro[7];
+    s.J_rot[1] = 0.f;
+    s.J_rot[2] = (float)(-ro[1]);
+    s.res_rot = res;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// kernel (b) part 1: ray sampling, in-ball test, ordered compaction (loss.py:60-70)
+// one warp per ray; sample j = 32*c + lane
+// ------------------------------------------------------------------------------------------------
+struct RayCtx {
+  const float* T;  // T_oc of the ray's object
+  float rx, ry, rz, d_min, d_max, step;
+};
+__device__ __forceinline__ RayCtx load_ray(const ObjState* st, int o, const float* __restrict__ rays, int r) {
+  RayCtx c;
+  c.T = st[o].T_oc;
+  c.rx = rays[r * 3 + 0]; c.ry = rays[r * 3 + 1]; c.rz = rays[r * 3 + 2];
+  c.d_min = st[o].d_min; c.d_max = st[o].d_max; c.step = st[o].delta_d;
+  return c;
+}
+
+template <bool FILL>
+__global__ void k_sample(const ObjState* __restrict__ st, const float* __restrict__ rays,
+                         const int* __restrict__ ray_obj, int R, int S, int* __restrict__ ray_cnt,
+                         const int* __restrict__ ray_base, float* __restrict__ q_pts, int* __restrict__ q_code) {
+  int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (r >= R) return;
+  int o = ray_obj[r];
+  if (st[o].failed) {
+    if (!FILL && lane == 0) ray_cnt[r] = 0;
+    return;
+  }
+  RayCtx c = load_ray(st, o, rays, r);
+  int base = FILL ? ray_base[r] : 0, cnt = 0;
+  for (int ch = 0; ch * 32 < S; ++ch) {
+    int j = ch * 32 + lane;
+    float x = 0, y = 0, z = 0;
+    bool in = false;
+    if (j < S) {
+      sample_point(c.T, c.rx, c.ry, c.rz, linspace_at(c.d_min, c.d_max, c.step, j, S), x, y, z);
+      in = in_ball(x, y, z);
+    }
+    unsigned m = __ballot_sync(0xffffffffu, in);
+    if (FILL && in) {
+      int idx = base + cnt + __popc(m & ((1u << lane) - 1u));
+      q_pts[idx * 3 + 0] = x; q_pts[idx * 3 + 1] = y; q_pts[idx * 3 + 2] = z;
+      q_code[idx] = o;
+    }
+    cnt += __popc(m);
+  }
+  if (!FILL && lane == 0) ray_cnt[r] = cnt;
+}
+
+// exclusive scan of n ints into out[0..n] (out[n] = total); single block, fixed order
+__global__ void k_exclusive_scan(const int* __restrict__ in, int* __restrict__ out, int n,
+                                 int* total, int total_add, int* total2) {
+  __shared__ int wsum[32];
+  __shared__ int carry_s;
+  int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  if (tid == 0) carry_s = 0;
+  __syncthreads();
+  for (int base = 0; base < n; base += blockDim.x) {
+    int i = base + tid;
+    int v = i < n ? in[i] : 0, x = v;
+    for (int d = 1; d < 32; d <<= 1) {
+      int y = __shfl_up_sync(0xffffffffu, x, d);
+      if (lane >= d) x += y;
+    }
+    if (lane == 31) wsum[w] = x;
+    __syncthreads();
+    if (w == 0) {
+      int s = lane < (blockDim.x >> 5) ? wsum[lane] : 0, t = s;
+      for (int d = 1; d < 32; d <<= 1) {
+        int y = __shfl_up_sync(0xffffffffu, t, d);
+        if (lane >= d) t += y;
+      }
+      wsum[lane] = t - s;
+    }
+    __syncthreads();
+    int carry = carry_s;
+    if (i < n) out[i] = carry + wsum[w] + x - v;
+    __syncthreads();
+    if (tid == blockDim.x - 1) carry_s = carry + wsum[w] + x;
+    __syncthreads();
+  }
+  if (tid == 0) {
+    out[n] = carry_s;
+    if (total) *total = carry_s;
+    if (total2) *total2 = carry_s + total_add;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// kernel (b) part 2: occupancy, transmittance scan, rendered depth, d e/d o, band selection
+// (loss.py:84-141).  One warp per ray.  Writes, per ray: the clamped depth residual and the number
+// of kept band samples; per (ray, sample) slot: de_ds of kept samples, 0 elsewhere.
+// ------------------------------------------------------------------------------------------------
+__global__ void k_render(ObjState* __restrict__ st, const float* __restrict__ rays,
+                         const int* __restrict__ ray_obj, const int* __restrict__ rays_off,
+                         const float* __restrict__ depth, const int* __restrict__ depth_off,
+                         int R, int S, float th, const int* __restrict__ ray_base,
+                         const float* __restrict__ q_sdf, float* __restrict__ slot_de_ds,
+                         float* __restrict__ ray_res, int* __restrict__ band_cnt) {
+  int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (r >= R) return;
+  int o = ray_obj[r];
+  if (st[o].failed) {
+    if (lane == 0) band_cnt[r] = 0;
+    return;
+  }
+  RayCtx c = load_ray(st, o, rays, r);
+  const int nc = (S + 31) >> 5;
+  float occ[GN_MAXC], T[GN_MAXC], dj[GN_MAXC];
+  bool band[GN_MAXC];
+  int cnt = 0, base = ray_base[r];
+  const float inv2th = 2.f * th;
+  // occupancy per sample; samples outside the ball keep occupancy 0 (loss.py:84-86)
+#pragma unroll
+  for (int ch = 0; ch < GN_MAXC; ++ch) {
+    occ[ch] = 0.f; band[ch] = false; dj[ch] = 0.f;
+    if (ch < nc) {
+      int j = ch * 32 + lane;
+      bool in = false;
+      if (j < S) {
+        float x, y, z;
+        dj[ch] = linspace_at(c.d_min, c.d_max, c.step, j, S);
+        sample_point(c.T, c.rx, c.ry, c.rz, dj[ch], x, y, z);
+        in = in_ball(x, y, z);
+      }
+      unsigned m = __ballot_sync(0xffffffffu, in);
+      if (in) {
+        float s = q_sdf[base + cnt + __popc(m & ((1u << lane) - 1u))];
+        occ[ch] = __fsub_rn(0.5f, __fdiv_rn(fminf(fmaxf(s, -th), th), inv2th));  // loss_utils.py:46-47
+        band[ch] = (s > -th) && (s < th);                                        // loss.py:88
+      }
+      cnt += __popc(m);
+    }
+  }
+  // transmittance T_j = prod_{l<=j} (1 - o_l)  (loss.py:99) and rendered depth (loss.py:100-114)
+  float carry = 1.f, du = 0.f;
+#pragma unroll
+  for (int ch = 0; ch < GN_MAXC; ++ch) {
+    if (ch < nc) {
+      float v = 1.f - occ[ch], x = v;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        float y = __shfl_up_sync(0xffffffffu, x, d);
+        if (lane >= d) x *= y;
+      }
+      float incl = carry * x;
+      float prev = __shfl_up_sync(0xffffffffu, incl, 1);
+      if (lane == 0) prev = carry;
+      int j = ch * 32 + lane;
+      T[ch] = j < S ? incl : 0.f;
+      du += (j < S) ? dj[ch] * (occ[ch] * prev) : 0.f;
+      carry = __shfl_sync(0xffffffffu, incl, 31);
+    }
+  }
+  du = warp_sum(du);
+  du += (1.1f * c.d_max) * carry;                      // o_S = 1 at d_S = 1.1 d_max
+  // suffix sums of T (loss.py:119-122) by a reverse scan, then de_do and the keep test (:125)
+  float tail = 0.f;
+  int kept = 0;
+  int rl = r - rays_off[o];
+  int K = depth_off[o + 1] - depth_off[o];
+  float dobs = rl < K ? depth[depth_off[o] + rl] : 1.1f * c.d_max;   // optimizer.py:153
+  float res = fminf(fmaxf(dobs - du, -0.30f), 0.30f);                // loss.py:136-140
+#pragma unroll
+  for (int ch = GN_MAXC - 1; ch >= 0; --ch) {
+    if (ch < nc) {
+      float x = T[ch];
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        float y = __shfl_down_sync(0xffffffffu, x, d);
+        if (lane + d < 32) x += y;
+      }
+      float suf = x + tail;
+      tail = __shfl_sync(0xffffffffu, suf, 0);
+      int j = ch * 32 + lane;
+      float out = 0.f;
+      if (band[ch]) {
+        float de_do = suf / (1.f - occ[ch]);
+        if (de_do > 1e-2f) out = (de_do * c.step) * (-1.f / (2.f * th));      // loss.py:128-130
+      }
+      if (j < S) slot_de_ds[(size_t)r * S + j] = out;
+      kept += __popc(__ballot_sync(0xffffffffu, out != 0.f));
+    }
+  }
+  int nband = 0;
+#pragma unroll
+  for (int ch = 0; ch < GN_MAXC; ++ch) nband += __popc(__ballot_sync(0xffffffffu, band[ch]));
+  if (lane == 0) {
+    band_cnt[r] = kept;
+    ray_res[r] = res;
+    atomicAdd(&st[o].n_inball, cnt);
+    atomicAdd(&st[o].n_band, nband);
+    atomicAdd(&st[o].n_keep, kept);
+  }
+}
+
+// writes the kept band points behind the surface points in the Jacobian row list (ray-major order,
+// as torch.where gives it: loss.py:68,89-90,133-134,143)
+__global__ void k_band_fill(const ObjState* __restrict__ st, const float* __restrict__ rays,
+                            const int* __restrict__ ray_obj, int R, int S,
+                            const float* __restrict__ slot_de_ds, const float* __restrict__ ray_res,
+                            const int* __restrict__ band_base, int row0, float* __restrict__ jp_pts,
+                            int* __restrict__ jp_code, float* __restrict__ row_fac,
+                            float* __restrict__ row_res, int* __restrict__ row_ray, int* __restrict__ row_samp) {
+  int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (r >= R) return;
+  int o = ray_obj[r];
+  if (st[o].failed) return;
+  if (band_base[r + 1] == band_base[r]) return;
+  RayCtx c = load_ray(st, o, rays, r);
+  int cnt = 0;
+  float res = ray_res[r];
+  for (int ch = 0; ch * 32 < S; ++ch) {
+    int j = ch * 32 + lane;
+    float f = j < S ? slot_de_ds[(size_t)r * S + j] : 0.f;
+    unsigned m = __ballot_sync(0xffffffffu, f != 0.f);
+    if (f != 0.f) {
+      int row = row0 + band_base[r] + cnt + __popc(m & ((1u << lane) - 1u));
+      float x, y, z;
+      sample_point(c.T, c.rx, c.ry, c.rz, linspace_at(c.d_min, c.d_max, c.step, j, S), x, y, z);
+      jp_pts[row * 3 + 0] = x; jp_pts[row * 3 + 1] = y; jp_pts[row * 3 + 2] = z;
+      jp_code[row] = o;
+      row_fac[row] = f;
+      row_res[row] = res;
+      row_ray[row] = r;
+      row_samp[row] = j;
+    }
+    cnt += __popc(m);
+  }
+}
+
+// surface points to the object frame (loss.py:31-32); rows [0, M_total) of the Jacobian row list
+__global__ void k_surface_xform(const ObjState* __restrict__ st, const float* __restrict__ pts,
+                                const int* __restrict__ pt_obj, int M, float* __restrict__ jp_pts,
+                                int* __restrict__ jp_code) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= M) return;
+  int o = pt_obj[i];
+  const float* T = st[o].T_oc;
+  float x, y, z;
+  sample_point(T, pts[i * 3], pts[i * 3 + 1], pts[i * 3 + 2], 1.0f, x, y, z);
+  jp_pts[i * 3] = x; jp_pts[i * 3 + 1] = y; jp_pts[i * 3 + 2] = z;
+  jp_code[i] = o;
+}
+
+// ------------------------------------------------------------------------------------------------
+// kernel (c): chain rule with the Sim(3) point Jacobian (loss_utils.py:166-185, loss.py:36-41,
+// 145-150), Huber re-weighting of the residual (loss_utils.py:236-265) and accumulation of the
+// upper triangle of [J r]^T [J r] (72x72: H, J^T r and sum r^2 in one pass; optimizer.py:217-226).
+// grid = (chunks, objects, 2 terms); partial sums are written per chunk and reduced in a fixed
+// order by k_solve, so the result is deterministic.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float huber_weight(float r, float b) {
+  float a = fabsf(r);
+  float nrm = a <= b ? a * a : 2.f * b * a - b * b;
+  float den = a == 0.f ? 1.f : a;
+  return sqrtf(nrm) / den;
+}
+
+__global__ void __launch_bounds__(256)
+k_accumulate(const ObjState* __restrict__ st, const int* __restrict__ pts_off,
+             const int* __restrict__ rays_off, const int* __restrict__ band_base, int M_total,
+             const float* __restrict__ jp_pts, const float* __restrict__ g_sdf,
+             const float* __restrict__ g_jac, const float* __restrict__ row_fac,
+             const float* __restrict__ row_res, float b_sdf, float b_render, int pose_only,
+             const float* __restrict__ row_active, float* __restrict__ partials) {
+  __shared__ float J[GN_SLOT][73];
+  const int chunk = blockIdx.x, nchunk = gridDim.x, o = blockIdx.y, term = blockIdx.z;
+  const int tid = threadIdx.x;
+  float* out = partials + (((size_t)o * 2 + term) * nchunk + chunk) * QSP_PART_STRIDE;
+  int start, count;
+  if (term == 0) { start = pts_off[o]; count = pts_off[o + 1] - start; }
+  else { start = M_total + band_base[rays_off[o]]; count = band_base[rays_off[o + 1]] - band_base[rays_off[o]]; }
+  const int lo = start + (int)((long)count * chunk / nchunk), hi = start + (int)((long)count * (chunk + 1) / nchunk);
+
+  // this thread's entries e = tid + 256*u of the row-major upper triangle of the 72x72 matrix
+  int ei[11], ej[11];
+  float acc[11];
+#pragma unroll
+  for (int u = 0; u < 11; ++u) {
+    int e = tid + 256 * u, i = 0;
+    acc[u] = 0.f;
+    if (e < 2628) {
+      while (e >= 72 - i) { e -= 72 - i; ++i; }
+      ei[u] = i; ej[u] = i + e;
+    } else { ei[u] = -1; ej[u] = 0; }
+  }
+  const bool dead = st[o].failed != 0;
+  for (int base = lo; base < hi && !dead; base += GN_SLOT) {
+    const int nr = min(GN_SLOT, hi - base);
+    __syncthreads();
+    // stage [J_pose(7) | J_code(64) | robust residual] for nr rows
+    for (int v = tid; v < nr * 72; v += 256) {
+      int rr = v / 72, c = v - rr * 72, row = base + rr;
+      const float* g = g_jac + (size_t)row * QSP_JSTRIDE;
+      float fac = term == 0 ? 1.f : row_fac[row];
+      if (row_active) fac *= row_active[row];          // pruned surface points (optimizer.py:80-82)
+      float val;
+      if (c >= 7 && c < 71) val = fac * g[c - 7];
+      else if (c == 71) {
+        float r = term == 0 ? g_sdf[row] : row_res[row];
+        val = pose_only ? r : huber_weight(r, term == 0 ? b_sdf : b_render) * r;
+        if (row_active) val *= row_active[row];
+      } else {
+        float g0 = fac * g[64], g1 = fac * g[65], g2 = fac * g[66];
+        float x = jp_pts[row * 3], y = jp_pts[row * 3 + 1], z = jp_pts[row * 3 + 2];
+        val = c == 0 ? g0 : c == 1 ? g1 : c == 2 ? g2
+            : c == 3 ? g1 * (-z) + g2 * y
+            : c == 4 ? g0 * z + g2 * (-x)
+            : c == 5 ? g0 * (-y) + g1 * x
+                     : g0 * x + g1 * y + g2 * z;
+      }
+      J[rr][c] = val;
+    }
+    __syncthreads();
+    for (int rr = 0; rr < nr; ++rr) {
+#pragma unroll
+      for (int u = 0; u < 11; ++u)
+        if (ei[u] >= 0) acc[u] = fmaf(J[rr][ei[u]], J[rr][ej[u]], acc[u]);
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < 11; ++u)
+    if (ei[u] >= 0) out[tid + 256 * u] = acc[u];
+}
+
+// ------------------------------------------------------------------------------------------------
+// exp maps (loss_utils.py:129-163, 188-233), fp32, branch for branch
+// ------------------------------------------------------------------------------------------------
+__device__ inline void exp_sim3_dev(const float* x, float* M, bool se3) {
+  float v[3] = {x[0], x[1], x[2]}, w[3] = {x[3], x[4], x[5]};
+  float s = se3 ? 0.f : x[6];
+  float wh[9] = {0.f, -w[2], w[1], w[2], 0.f, -w[0], -w[1], w[0], 0.f}, wh2[9];
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 3; ++c)
+      wh2[r * 3 + c] = wh[r * 3] * wh[c] + wh[r * 3 + 1] * wh[3 + c] + wh[r * 3 + 2] * wh[6 + c];
+  float th = sqrtf(w[0] * w[0] + w[1] * w[1] + w[2] * w[2]);
+  float th2 = th * th, sn = sinf(th), cs = cosf(th), es = se3 ? 1.f : expf(s), s2 = s * s;
+  float ew[9], jm[9];
+  const float eye[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+  if (th <= 1e-8f) {
+    float c = (se3 || s == 0.f) ? 1.f : (es - 1.f) / s;
+    for (int i = 0; i < 9; ++i) { ew[i] = eye[i]; jm[i] = c * eye[i]; }
+  } else if (se3) {
+    float k1 = (1.f - cs) / th2, k2 = (th - sn) / (th2 * th);
+    for (int i = 0; i < 9; ++i) {
+      ew[i] = eye[i] + wh[i] * sn / th + wh2[i] * (1.f - cs) / th2;
+      jm[i] = eye[i] + k1 * wh[i] + k2 * wh2[i];
+    }
+  } else {
+    float a = es * sn, b = es * cs;
+    float c = s <= 1e-8f ? 0.f : (es - 1.f) / s;       // loss_utils.py:223 (also 0 for negative s)
+    float k1 = (a * s + (1.f - b) * th) / (s2 + th2);
+    float k2 = c - ((b - 1.f) * s + a * th) / (s2 + th2);
+    for (int i = 0; i < 9; ++i) {
+      ew[i] = eye[i] + wh[i] * sn / th + wh2[i] * (1.f - cs) / th2;
+      jm[i] = c * eye[i] + k1 * wh[i] / th + k2 * wh2[i] / th2;
+    }
+  }
+  for (int r = 0; r < 3; ++r) {
+    for (int c = 0; c < 3; ++c) M[r * 4 + c] = es * ew[r * 3 + c];
+    M[r * 4 + 3] = jm[r * 3] * v[0] + jm[r * 3 + 1] * v[1] + jm[r * 3 + 2] * v[2];
+  }
+  M[12] = M[13] = M[14] = 0.f;
+  M[15] = 1.f;
+}
+
+// ------------------------------------------------------------------------------------------------
+// kernel (d): per-object reduction of the partial sums, assembly of the damped normal equations
+// (optimizer.py:205,218-252), Cholesky solve (the reference inverts H with LAPACK on the CPU, :254;
+// H is SPD after damping so the solutions agree to rounding), exp map and state update (:261-263).
+// One CTA per object.  `ndof` = 71 (joint) or 6 (pose only, optimizer.py:72-78).
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128)
+k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
+        const float* __restrict__ partials, GnParamsDev p, int pose_only,
+        const int* __restrict__ m_active, float* __restrict__ dbg_H, float* __restrict__ dbg_b, float* __restrict__ dbg_dx) {
+  __shared__ double A[72][73];
+  __shared__ double rhs[72];
+  __shared__ float dxs[72];
+  __shared__ int fail_s;
+  const int o = blockIdx.x, tid = threadIdx.x;
+  ObjState& s = st[o];
+  if (s.failed) return;
+  const int M = m_active ? m_active[o] : pts_off[o + 1] - pts_off[o], P = s.n_keep, Q = s.n_inball;
+  const int n = pose_only ? 6 : 71;
+  const float ws = pose_only ? 1.f : p.k2, wr = pose_only ? 0.f : p.k1;
+  // fixed-order reduction of the chunk partials; entry e of the 72x72 upper triangle
+  for (int e = tid; e < 2628; e += 128) {
+    float ss = 0.f, sr = 0.f;
+    for (int c = 0; c < nchunk; ++c) {
+      ss += partials[(((size_t)o * 2 + 0) * nchunk + c) * QSP_PART_STRIDE + e];
+      if (!pose_only) sr += partials[(((size_t)o * 2 + 1) * nchunk + c) * QSP_PART_STRIDE + e];
+    }
+    int i = 0, r = e;
+    while (r >= 72 - i) { r -= 72 - i; ++i; }
+    int j = i + r;
+    float v = pose_only ? ss / (float)M : wr * sr / (float)P + ws * ss / (float)M;
+    A[i][j] = (double)v;                                // fp32 values, held exactly
+    A[j][i] = (double)v;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    float loss = (float)A[71][71];                            // k1*render_loss + k2*sdf_loss (optimizer.py:205)
+    int f = 0;
+    if (!pose_only && (Q < 10 || P == 0 || isnan(loss))) f = 1;   // loss.py:73-74, optimizer.py:168,193
+    if (pose_only && M == 0) f = 1;
+    fail_s = f;
+    if (f) s.failed = 1; else s.loss = loss;
+  }
+  __syncthreads();
+  if (fail_s) return;
+  // b = -J^T r ; regulariser, rotation prior, damping
+  if (tid < n) {
+    float b = -(float)A[tid][71];
+    if (!pose_only) {
+      if (tid >= 7) b -= p.k3 * s.code[tid - 7];                         // optimizer.py:234
+      else if (tid >= 3 && tid < 6) b += p.k4 * s.J_rot[tid - 3] * s.res_rot;  // :242-244
+    }
+    rhs[tid] = (double)b;
+  }
+  __syncthreads();
+  for (int v = tid; v < n * n; v += 128) {
+    int i = v / n, j = v - i * n;
+    float h = (float)A[i][j];
+    if (pose_only) { if (i == j) h += 1e-2f; }                           // optimizer.py:74
+    else {
+      if (i == j && i >= 7) h += p.k3;                                   // :232
+      if (i >= 3 && i < 6 && j >= 3 && j < 6) h += p.k4 * (s.J_rot[i - 3] * s.J_rot[j - 3]);  // :241,243
+      if (i == j && i < 7) h += 1.0f;                                    // :251
+      if (i == 6 && j == 6) h += p.s_damp;                               // :252
+    }
+    A[i][j] = (double)h;
+    if (dbg_H) dbg_H[(size_t)o * 71 * 71 + i * 71 + j] = h;
+  }
+  if (dbg_b && tid < n) dbg_b[o * 71 + tid] = (float)rhs[tid];
+  __syncthreads();
+  // in-place Cholesky A = L L^T (lower), fp64
+  for (int k = 0; k < n; ++k) {
+    if (tid == 0) A[k][k] = sqrt(A[k][k]);
+    __syncthreads();
+    if (tid > k && tid < n) A[tid][k] /= A[k][k];
+    __syncthreads();
+    for (int v = tid; v < (n - k - 1) * (n - k - 1); v += 128) {
+      int i = k + 1 + v / (n - k - 1), j = k + 1 + v % (n - k - 1);
+      if (j <= i) A[i][j] -= A[i][k] * A[j][k];
+    }
+    __syncthreads();
+  }
+  if (tid == 0) {
+    for (int i = 0; i < n; ++i) {
+      double t = rhs[i];
+      for (int j = 0; j < i; ++j) t -= A[i][j] * rhs[j];
+      rhs[i] = t / A[i][i];
+    }
+    for (int i = n - 1; i >= 0; --i) {
+      double t = rhs[i];
+      for (int j = i + 1; j < n; ++j) t -= A[j][i] * rhs[j];
+      rhs[i] = t / A[i][i];
+    }
+  }
+  __syncthreads();
+  if (tid < n) {
+    dxs[tid] = (float)rhs[tid];
+    if (dbg_dx) dbg_dx[o * 71 + tid] = dxs[tid];
+  }
+  __syncthreads();
+  if (!pose_only && tid >= 7 && tid < 71) s.code[tid - 7] += p.lr * dxs[tid];     // optimizer.py:263
+  if (tid == 0) {
+    float x[7], D[16], N[16];
+    for (int i = 0; i < 7; ++i) x[i] = i < n ? (pose_only ? dxs[i] : p.lr * dxs[i]) : 0.f;
+    exp_sim3_dev(x, D, pose_only != 0);
+    for (int r = 0; r < 4; ++r)
+      for (int c = 0; c < 4; ++c) {
+        float t = 0.f;
+        for (int k = 0; k < 4; ++k) t += D[r * 4 + k] * s.T_oc[k * 4 + c];
+        N[r * 4 + c] = t;
+      }
+    for (int i = 0; i < 16; ++i) s.T_oc[i] = N[i];                                 // optimizer.py:262
+  }
+}
+
+// records: t_cam_obj (16) | code (64) | is_good | loss  (optimizer.py:274-281)
+__global__ void k_finalize(const ObjState* __restrict__ st, int B, float* __restrict__ records) {
+  int o = blockIdx.x * blockDim.x + threadIdx.x;
+  if (o >= B) return;
+  const ObjState& s = st[o];
+  float* r = records + (size_t)o * 82;
+  float T[16];
+  const float nanv = __int_as_float(0x7fc00000);
+  if (!s.failed) inv_affine(s.T_oc, T);
+  for (int i = 0; i < 16; ++i) r[i] = s.failed ? nanv : T[i];
+  for (int i = 0; i < 64; ++i) r[16 + i] = s.failed ? nanv : s.code[i];
+  r[80] = s.failed ? 0.f : 1.f;
+  r[81] = s.loss;
+}
+
+// inlier pruning of the pose-only loop: keep |res| <= 0.05 after iteration index 4 (optimizer.py:80-82)
+__global__ void k_prune(const float* __restrict__ g_sdf, const int* __restrict__ pt_obj, int M,
+                        float* __restrict__ row_active, int* __restrict__ m_active) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= M) return;
+  bool keep = row_active[i] != 0.f && fabsf(g_sdf[i]) <= 0.05f;
+  row_active[i] = keep ? 1.f : 0.f;
+  if (keep) atomicAdd(&m_active[pt_obj[i]], 1);
+}
+
+// pose-only set-up: T_oc = inverse([scale * R | t]) (optimizer.py:57-59); result conversion (:87-88)
+__global__ void k_init_pose_only(ObjState* st, const float* __restrict__ t_co_se3,
+                                 const float* __restrict__ scale, const float* __restrict__ codes, int B) {
+  int o = blockIdx.x * blockDim.x + threadIdx.x;
+  if (o >= B) return;
+  float T[16];
+  for (int i = 0; i < 16; ++i) T[i] = t_co_se3[o * 16 + i];
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 3; ++c) T[r * 4 + c] *= scale[o];
+  ObjState& s = st[o];
+  inv_affine(T, s.T_oc);
+  for (int c = 0; c < 64; ++c) s.code[c] = codes[o * 64 + c];
+  s.loss = 0.f; s.failed = 0; s.n_inball = s.n_band = s.n_keep = 0;
+}
+__global__ void k_finalize_pose_only(const ObjState* __restrict__ st, const float* __restrict__ scale,
+                                     int B, float* __restrict__ out) {
+  int o = blockIdx.x * blockDim.x + threadIdx.x;
+  if (o >= B) return;
+  float T[16];
+  inv_affine(st[o].T_oc, T);
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 3; ++c) T[r * 4 + c] /= scale[o];
+  for (int i = 0; i < 16; ++i) out[o * 16 + i] = T[i];
+}

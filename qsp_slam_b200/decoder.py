@@ -1,0 +1,129 @@
+"""Device-resident DeepSDF decoder handle.
+
+Takes the UNCHANGED deep_sdf state dict (``lin{l}.weight_g / weight_v / bias``, ``lin8.weight/bias``;
+deep_sdf/deep_sdf_decoder.py:41-63), with or without DataParallel's ``module.`` prefix
+(deep_sdf/workspace.py:215-219), folds weight norm inside the native library and keeps the operands
+on one GPU.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Optional
+
+import numpy as np
+
+from . import _native as N
+
+_IN = [67, 512, 512, 512, 512, 512, 512, 512, 512]
+_OUT = [512, 512, 512, 445, 512, 512, 512, 512, 1]
+
+
+def _to_numpy_state(obj) -> Dict[str, np.ndarray]:
+    if hasattr(obj, "state_dict"):
+        obj = obj.state_dict()
+    out = {}
+    for k, v in dict(obj).items():
+        if k.startswith("module."):
+            k = k[len("module."):]
+        if hasattr(v, "detach"):
+            v = v.detach().cpu().numpy()
+        out[k] = np.ascontiguousarray(v, dtype=np.float32)
+    return out
+
+
+class DeviceDecoder:
+    """Owns a ``qsp_decoder*``.  ``decoder`` may be a state dict, an ``nn.Module`` or another
+    ``DeviceDecoder`` (returned as is by :func:`as_device_decoder`)."""
+
+    def __init__(self, decoder, device: int = 0):
+        st = _to_numpy_state(decoder)
+        for l in range(8):
+            for key, shape in ((f"lin{l}.weight_v", (_OUT[l], _IN[l])), (f"lin{l}.weight_g", (_OUT[l], 1)),
+                               (f"lin{l}.bias", (_OUT[l],))):
+                if key not in st:
+                    raise KeyError(f"decoder state dict lacks '{key}' (expected the 8x512 weight-normed DeepSDF layout)")
+                if st[key].size != int(np.prod(shape)):
+                    raise ValueError(f"'{key}' has shape {st[key].shape}, expected {shape}")
+        if st["lin8.weight"].size != 512 or st["lin8.bias"].size != 1:
+            raise ValueError("lin8 must be 512 -> 1")
+        w = N.DecoderWeights()
+        self._keep = st
+        fp = C.POINTER(C.c_float)
+        for l in range(8):
+            w.weight_v[l] = st[f"lin{l}.weight_v"].ctypes.data_as(fp)
+            w.weight_g[l] = st[f"lin{l}.weight_g"].ctypes.data_as(fp)
+            w.bias[l] = st[f"lin{l}.bias"].ctypes.data_as(fp)
+        w.lin8_weight = st["lin8.weight"].ctypes.data_as(fp)
+        w.lin8_bias = st["lin8.bias"].ctypes.data_as(fp)
+        h = C.c_void_p()
+        N.check(N.lib().qsp_decoder_create(C.byref(w), int(device), C.byref(h)))
+        self.handle = h
+        self.device = int(device)
+        self.state = st
+
+    def close(self):
+        if getattr(self, "handle", None):
+            N.lib().qsp_decoder_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # nn.Module look-alikes so that reference-style call sites keep working
+    def eval(self):
+        return self
+
+    def cuda(self, *a, **k):
+        return self
+
+    # --- kernel (a) -------------------------------------------------------------------------------
+    def decode_sdf(self, codes, pts) -> np.ndarray:
+        """codes (C,64) or (64,), pts (n,3) host arrays -> (C,n) or (n,) float32  (loss_utils.py:51-79)."""
+        codes = N.f32(codes)
+        single = codes.ndim == 1
+        codes = codes.reshape(-1, 64)
+        pts = N.f32(pts)[:, :3]
+        pts = np.ascontiguousarray(pts)
+        out = np.empty((codes.shape[0], pts.shape[0]), np.float32)
+        if pts.shape[0]:
+            N.check(N.lib().qsp_decode_sdf(self.handle, N.ptr(codes), codes.shape[0], N.ptr(pts), pts.shape[0],
+                                           N.ptr(out), N.FLAG_HOST_PTRS, None))
+        return out[0] if single else out
+
+    def decode_sdf_device(self, codes, pts, out, sync: bool = True):
+        """Same with torch CUDA tensors (float32, contiguous); ``out`` (C,n) is written in place."""
+        n_codes = codes.numel() // 64
+        n = pts.shape[0]
+        N.check(N.lib().qsp_decode_sdf(self.handle, N.ptr(codes), n_codes, N.ptr(pts), n, N.ptr(out),
+                                       N.FLAG_SYNC if sync else 0, None))
+        return out
+
+    def decode_sdf_jacobian(self, code, pts):
+        """(sdf (n,), d sdf/d[code,xyz] (n,67)) - loss_utils.py:82-103."""
+        code = N.f32(code).reshape(64)
+        pts = np.ascontiguousarray(N.f32(pts)[:, :3])
+        n = pts.shape[0]
+        sdf = np.empty(n, np.float32)
+        jac = np.empty((n, N.JAC_STRIDE), np.float32)
+        if n:
+            N.check(N.lib().qsp_decode_sdf_jacobian(self.handle, N.ptr(code), N.ptr(pts), n, N.ptr(sdf), N.ptr(jac),
+                                                    N.FLAG_HOST_PTRS, None))
+        return sdf, jac[:, :67]
+
+    def decode_sdf_jacobian_device(self, code, pts, sdf, jac, sync: bool = True):
+        N.check(N.lib().qsp_decode_sdf_jacobian(self.handle, N.ptr(code), N.ptr(pts), pts.shape[0], N.ptr(sdf),
+                                                N.ptr(jac), N.FLAG_SYNC if sync else 0, None))
+
+    def last_kernel_ms(self) -> float:
+        ms = C.c_float()
+        N.check(N.lib().qsp_kernel_ms(self.handle, C.byref(ms)))
+        return float(ms.value)
+
+
+def as_device_decoder(decoder, device: Optional[int] = None) -> DeviceDecoder:
+    if isinstance(decoder, DeviceDecoder):
+        return decoder
+    return DeviceDecoder(decoder, 0 if device is None else device)

@@ -1,0 +1,57 @@
+"""The pieces of reconstruct/utils.py the hot path needs (ForceKeyErrorDict :82-84, get_configs :87-90,
+create_voxel_grid :98-117), without the addict / skimage / plyfile imports."""
+from __future__ import annotations
+
+import json
+
+import numpy as np
+
+
+class ForceKeyErrorDict(dict):
+    """Attribute-style dict that raises KeyError on a missing key (reference: addict.Dict subclass
+    whose ``__missing__`` raises, utils.py:82-84).  Nested dicts are wrapped on construction."""
+
+    def __init__(self, *a, **kw):
+        super().__init__()
+        for k, v in dict(*a, **kw).items():
+            self[k] = v
+
+    def __setitem__(self, k, v):
+        if isinstance(v, dict) and not isinstance(v, ForceKeyErrorDict):
+            v = ForceKeyErrorDict(v)
+        super().__setitem__(k, v)
+
+    def __getattr__(self, k):
+        try:
+            return self[k]
+        except KeyError:
+            raise KeyError(k)
+
+    def __setattr__(self, k, v):
+        self[k] = v
+
+    def __missing__(self, key):
+        raise KeyError(key)
+
+
+def get_configs(cfg_file):
+    with open(cfg_file) as f:
+        cfg_dict = json.load(f)
+    return ForceKeyErrorDict(**cfg_dict)
+
+
+def create_voxel_grid(vol_dim: int = 128) -> np.ndarray:
+    """(vol_dim^3, 3) float32 grid in [-1,1]^3 exactly as the reference builds it, INCLUDING its
+    true-division quirk (utils.py:106-107: ``index / vol_dim`` is not floored under torch >= 1.7, so
+    the first two columns carry fractional offsets).  The arithmetic is done in float32 like torch's
+    ``LongTensor / int -> float32`` promotion."""
+    voxel_size = 2.0 / (vol_dim - 1)
+    idx = np.arange(vol_dim ** 3, dtype=np.int64)
+    v = np.zeros((vol_dim ** 3, 3), np.float32)
+    q = idx.astype(np.float32) / np.float32(vol_dim)          # true division, fp32
+    v[:, 2] = (idx % vol_dim).astype(np.float32)
+    v[:, 1] = np.fmod(q, np.float32(vol_dim))
+    v[:, 0] = np.fmod(q / np.float32(vol_dim), np.float32(vol_dim))
+    for c in range(3):
+        v[:, c] = v[:, c] * np.float32(voxel_size) + np.float32(-1)
+    return v

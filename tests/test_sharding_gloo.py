@@ -1,0 +1,68 @@
+"""world_size-2 gloo test of the object-sharding host logic (no GPU): partition, gather, order."""
+import os
+import socket
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from qsp_slam_b200 import sharding
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, n_obj, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    costs = [(i % 5) + 1 for i in range(n_obj)]
+    ranks = sharding.balanced_order(costs, world)
+    mine = ranks[rank]
+    # fake per-object records: row i carries its object id everywhere
+    local = torch.tensor([[float(i)] * sharding.RECORD_LEN for i in mine], dtype=torch.float32).reshape(-1, sharding.RECORD_LEN)
+    allr = sharding.gather_records(local, [len(r) for r in ranks])
+    ordered = sharding.scatter_back(allr.numpy(), ranks)
+    if rank == 0:
+        q.put(ordered[:, 0].tolist())
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_partition_covers_everything():
+    for n in (0, 1, 7, 32, 1024):
+        for w in (1, 2, 4, 8):
+            p = sharding.partition(n, w)
+            assert p[0][0] == 0 and p[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(p, p[1:]))
+            sizes = [hi - lo for lo, hi in p]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def test_balanced_order_is_a_permutation_and_balanced():
+    costs = list(np.random.default_rng(0).integers(1, 100, 57))
+    r = sharding.balanced_order(costs, 4)
+    assert sorted(i for x in r for i in x) == list(range(57))
+    loads = [sum(costs[i] for i in x) for x in r]
+    assert max(loads) - min(loads) <= max(costs)
+
+
+def test_gather_two_ranks_gloo():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    n_obj = 11
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, n_obj, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = q.get(timeout=120)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert got == [float(i) for i in range(n_obj)]
