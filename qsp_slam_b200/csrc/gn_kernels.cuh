@@ -80,8 +80,12 @@ __global__ void k_prep(ObjState* st, int B, int S) {
   if (o >= B) return;
   ObjState& s = st[o];
   if (s.failed) return;
-  float det = inv_affine(s.T_oc, s.T_co);
-  float scale = cbrtf(det);
+  inv_affine(s.T_oc, s.T_co);
+  const float* C = s.T_co;                             // scale = det(T_co[:3,:3]) ** (1/3)  (optimizer.py:148)
+  double det = (double)C[0] * ((double)C[5] * C[10] - (double)C[6] * C[9]) -
+               (double)C[1] * ((double)C[4] * C[10] - (double)C[6] * C[8]) +
+               (double)C[2] * ((double)C[4] * C[9] - (double)C[5] * C[8]);
+  float scale = cbrtf((float)det);
   s.scale = scale;
   s.d_min = __fsub_rn(s.T_co[11], scale);
   s.d_max = __fadd_rn(s.T_co[11], scale);
