@@ -36,8 +36,16 @@ typedef enum qsp_status {
 
 enum {
   QSP_FLAG_HOST_PTRS = 1,    /* data pointers are host memory; the call copies h2d/d2h itself */
-  QSP_FLAG_SYNC = 2          /* cudaStreamSynchronize before returning */
+  QSP_FLAG_SYNC = 2,         /* cudaStreamSynchronize before returning */
+  QSP_FLAG_FAST_FP16 = 4,    /* qsp_decode_sdf only: single-pass fp16 operands (|err| ~ 3e-4), 3-4x faster */
+  QSP_FLAG_FP32_CORES = 8    /* decode calls: exact-fp32 CUDA-core kernel instead of the tensor-core one */
 };
+
+/* Arithmetic of the decoder inside the GN loop.  TENSOR (default): tcgen05 tensor-core kernel with
+ * every operand carried as an fp16 (hi, lo) pair and fp32 accumulation (fp32-equivalent); ray
+ * samples far from the +-cut_off band are classified by a single-pass fp16 evaluation first.
+ * FP32_CORES: the same pipeline on the exact-fp32 CUDA-core kernel (validation / A-B testing).  */
+typedef enum qsp_precision { QSP_PREC_TENSOR = 0, QSP_PREC_FP32_CORES = 1 } qsp_precision;
 
 /* Decoder parameters exactly as the deep_sdf state dict holds them
  * (deep_sdf/deep_sdf_decoder.py:41-63): lin0..lin7 weight-normed, lin8 plain.
@@ -68,6 +76,8 @@ typedef struct qsp_decoder qsp_decoder; /* opaque: folded weights on one device 
 /* --- lifetime: replaces deep_sdf/workspace.py:202-224 config_decoder (weights -> device) ------ */
 int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_decoder** out);
 void qsp_decoder_destroy(qsp_decoder* dec);
+
+int qsp_set_precision(qsp_decoder* dec, int32_t precision);
 
 /* --- kernel (a), forward only: replaces reconstruct/loss_utils.py:51-79 decode_sdf ----------- */
 /* out[c*n + i] = sdf(codes[c], pts[i]);  codes (n_codes,64), pts (n,3), out (n_codes,n).       */

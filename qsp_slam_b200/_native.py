@@ -12,12 +12,17 @@ LIB_PATH = os.path.join(HERE, "libqsp_recon.so")
 
 FLAG_HOST_PTRS = 1
 FLAG_SYNC = 2
+FLAG_FAST_FP16 = 4
+FLAG_FP32_CORES = 8
+PREC_TENSOR = 0
+PREC_FP32_CORES = 1
+MODE_FLAGS = {"tensor": 0, "fast": FLAG_FAST_FP16, "fp32": FLAG_FP32_CORES}
 CODE_LEN = 64
 JAC_STRIDE = 68
 RECORD_LEN = 82
 
 EXPORTS = ["qsp_decoder_create", "qsp_decoder_destroy", "qsp_decode_sdf", "qsp_decode_sdf_jacobian",
-           "qsp_reconstruct_batch", "qsp_estimate_pose_batch", "qsp_set_debug", "qsp_get_iteration",
+           "qsp_reconstruct_batch", "qsp_estimate_pose_batch", "qsp_set_precision", "qsp_set_debug", "qsp_get_iteration",
            "qsp_get_band_indices", "qsp_last_error", "qsp_launch_count", "qsp_kernel_ms", "qsp_version"]
 
 _f32p = C.POINTER(C.c_float)
@@ -61,6 +66,7 @@ def lib():
                                         vp, _i32p, vp, C.c_uint32, vp]
     L.qsp_estimate_pose_batch.argtypes = [vp, C.c_int32, C.c_int32, vp, vp, vp, vp, _i32p, vp, C.c_uint32, vp]
     L.qsp_set_debug.argtypes = [vp, C.c_int32]
+    L.qsp_set_precision.argtypes = [vp, C.c_int32]
     L.qsp_get_iteration.argtypes = [vp, C.c_int32, C.c_int32, vp, vp, vp, vp]
     L.qsp_get_band_indices.argtypes = [vp, C.c_int32, C.c_int32, vp, vp, C.c_int32]
     L.qsp_last_error.restype = C.c_char_p

@@ -1,5 +1,6 @@
 // C ABI of the reconstruction path (include/qsp_recon.h): handle, weight folding, workspace and the
 // per-iteration launch sequence.  Host code only orchestrates; all arithmetic is in the kernels.
+#include <cuda_fp16.h>
 #include <atomic>
 #include <cmath>
 #include <cstdio>
@@ -9,6 +10,7 @@
 
 #include "../../include/qsp_recon.h"
 #include "decoder_ffma.cuh"
+#include "decoder_tc.cuh"
 #include "gn_kernels.cuh"
 
 static thread_local std::string g_err;
@@ -39,6 +41,8 @@ struct qsp_decoder {
   int device = 0;
   int num_sms = 148;
   DecoderDev dw{};
+  TcDecoderDev tc{};
+  int precision = QSP_PREC_TENSOR;     // arithmetic of kernel (a) inside the GN loop
   std::vector<void*> weight_allocs;
   // workspace (grown on demand, owned by the handle)
   Buf in_T, in_code, in_pts, in_rays, in_depth, in_scale, out_rec;
@@ -99,6 +103,68 @@ static int upload(qsp_decoder* d, const std::vector<float>& h, const float** dev
   return QSP_OK;
 }
 
+// One [256 n][64 k] fp16 operand image in the K-major SWIZZLE_128B layout the UMMA descriptor expects:
+// byte offset of (n, k) = (n/8)*1024 + (n%8)*128 + (((k/8) ^ (n%8)) * 16) + (k%8)*2.
+template <class F>
+static void put_tile(std::vector<__half>& hi, std::vector<__half>* lo, size_t tile, float scale, F src) {
+  for (int n = 0; n < 256; ++n)
+    for (int k = 0; k < 64; ++k) {
+      size_t off = tile * (TC_TILE_BYTES / 2) + ((n / 8) * 1024 + (n % 8) * 128 + (((k / 8) ^ (n % 8)) * 16) + (k % 8) * 2) / 2;
+      float v = scale * src(n, k);
+      __half h = __float2half_rn(v);
+      hi[off] = h;
+      if (lo) (*lo)[off] = __float2half_rn(v - __half2float(h));
+    }
+}
+
+// Weight streams in the exact order k_decoder_tc consumes them (step, half, k-block[, hi, lo]).
+static int build_tc_images(qsp_decoder* d, const std::vector<std::vector<float>>& W) {
+  auto w_at = [&](int l, int o, int i) -> float { return (o < kOut[l] && i < kIn[l]) ? W[l][(size_t)o * kIn[l] + i] : 0.f; };
+  size_t n_fast = 0, n_split = 0;
+  for (int s = 0; s < 16; ++s) {
+    int tiles = (s == 15 ? 1 : 2) * (s == 0 ? 2 : 8);
+    if (s < 8) n_fast += tiles;
+    n_split += 2 * tiles;
+  }
+  std::vector<__half> fast(n_fast * (TC_TILE_BYTES / 2)), split(n_split * (TC_TILE_BYTES / 2));
+  size_t tf = 0, ts = 0;
+  for (int s = 0; s < 16; ++s) {
+    const bool fwd = s < 8;
+    const int l = fwd ? s : 15 - s, nh = s == 15 ? 1 : 2, nkb = s == 0 ? 2 : 8;
+    for (int h = 0; h < nh; ++h)
+      for (int kb = 0; kb < nkb; ++kb) {
+        auto src = [&](int n, int k) -> float {
+          return fwd ? w_at(l, h * 256 + n, kb * 64 + k)      // B[n = out][k = in]
+                     : w_at(l, kb * 64 + k, h * 256 + n);     // B[n = in][k = out]
+        };
+        if (fwd) put_tile(fast, nullptr, tf++, 1.f, src);
+        std::vector<__half> lo_tmp;  // hi and lo tiles are adjacent in the split stream
+        {
+          // write hi into tile ts, lo into tile ts+1
+          for (int n = 0; n < 256; ++n)
+            for (int k = 0; k < 64; ++k) {
+              size_t in_tile = ((n / 8) * 1024 + (n % 8) * 128 + (((k / 8) ^ (n % 8)) * 16) + (k % 8) * 2) / 2;
+              float v = TC_SW * src(n, k);
+              __half hh = __float2half_rn(v);
+              split[ts * (TC_TILE_BYTES / 2) + in_tile] = hh;
+              split[(ts + 1) * (TC_TILE_BYTES / 2) + in_tile] = __float2half_rn(v - __half2float(hh));
+            }
+          ts += 2;
+        }
+      }
+  }
+  void *pf = nullptr, *ps = nullptr;
+  CK(cudaMalloc(&pf, fast.size() * 2));
+  d->weight_allocs.push_back(pf);
+  CK(cudaMalloc(&ps, split.size() * 2));
+  d->weight_allocs.push_back(ps);
+  CK(cudaMemcpy(pf, fast.data(), fast.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(ps, split.data(), split.size() * 2, cudaMemcpyHostToDevice));
+  d->tc.img_fast = reinterpret_cast<const uint8_t*>(pf);
+  d->tc.img_split = reinterpret_cast<const uint8_t*>(ps);
+  return QSP_OK;
+}
+
 extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_decoder** out) {
   if (!w || !out) { g_err = "null argument"; return QSP_ERR_INVALID; }
   int ndev = 0;
@@ -116,10 +182,14 @@ extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_
   qsp_decoder* d = new qsp_decoder();
   d->device = device;
   d->num_sms = prop.multiProcessorCount;
+  std::vector<std::vector<float>> Wall(8);
+  std::vector<float> bias_all(8 * 512, 0.f);
   for (int l = 0; l < 8; ++l) {
     const int in = kIn[l], on = kOut[l];
     const int kpad = l == 0 ? 80 : 512;
-    std::vector<float> W((size_t)on * in), Wf((size_t)kpad * 512, 0.f), Wb((size_t)512 * 512, 0.f), bias(512, 0.f);
+    std::vector<float>& W = Wall[l];
+    W.resize((size_t)on * in);
+    std::vector<float> Wf((size_t)kpad * 512, 0.f), Wb((size_t)512 * 512, 0.f), bias(512, 0.f);
     for (int o = 0; o < on; ++o) {
       const float* v = w->weight_v[l] + (size_t)o * in;
       double nn = 0;
@@ -127,6 +197,7 @@ extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_
       float scale = w->weight_g[l][o] / (float)std::sqrt(nn);
       for (int i = 0; i < in; ++i) W[(size_t)o * in + i] = v[i] * scale;
       bias[o] = w->bias[l][o];
+      bias_all[l * 512 + o] = w->bias[l][o];
     }
     for (int o = 0; o < on; ++o)
       for (int i = 0; i < in; ++i) {
@@ -144,6 +215,12 @@ extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_
   int r = upload(d, w8, &d->dw.w8);
   if (r) { qsp_decoder_destroy(d); return r; }
   d->dw.b8 = w->lin8_bias[0];
+  if ((r = build_tc_images(d, Wall)) || (r = upload(d, bias_all, &d->tc.bias))) { qsp_decoder_destroy(d); return r; }
+  d->tc.w8 = d->dw.w8;
+  d->tc.b8 = d->dw.b8;
+  CK(cudaFuncSetAttribute(k_decoder_tc<TC_FAST, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+  CK(cudaFuncSetAttribute(k_decoder_tc<TC_SPLIT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+  CK(cudaFuncSetAttribute(k_decoder_tc<TC_SPLIT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
   CK(cudaFuncSetAttribute(k_decoder_ffma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FF_SMEM_BYTES));
   CK(cudaFuncSetAttribute(k_decoder_ffma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FF_SMEM_BYTES));
   CK(cudaEventCreate(&d->ev0));
@@ -169,6 +246,12 @@ extern "C" void qsp_decoder_destroy(qsp_decoder* d) {
   delete d;
 }
 
+extern "C" int qsp_set_precision(qsp_decoder* d, int32_t precision) {
+  if (!d || (precision != QSP_PREC_TENSOR && precision != QSP_PREC_FP32_CORES)) { g_err = "bad precision"; return QSP_ERR_INVALID; }
+  d->precision = precision;
+  return QSP_OK;
+}
+
 extern "C" int qsp_kernel_ms(qsp_decoder* d, float* ms) {
   if (!d || !ms) return QSP_ERR_INVALID;
   *ms = d->last_ms;
@@ -178,12 +261,26 @@ extern "C" int qsp_kernel_ms(qsp_decoder* d, float* ms) {
 // ------------------------------------------------------------------------------------------------
 // kernel (a) entry points
 // ------------------------------------------------------------------------------------------------
-static int launch_decoder(qsp_decoder* d, bool jac, const float* pts, const int* code_idx, const float* codes,
+enum DecMode { DEC_FP32 = 0, DEC_SPLIT = 1, DEC_FAST = 2 };
+
+static int launch_decoder(qsp_decoder* d, int mode, bool jac, const float* pts, const int* code_idx, const float* codes,
                           int code_stride, long n, const int* n_dev, int n_codes_y, float* sdf, float* jacp,
                           cudaStream_t st) {
-  long tiles = n_dev ? (long)d->num_sms : ((n + FF_TILE - 1) / FF_TILE) * n_codes_y;
+  const int rows_per_tile = mode == DEC_FAST ? 128 : 64;
+  long tiles = n_dev ? (long)d->num_sms : ((n + rows_per_tile - 1) / rows_per_tile) * n_codes_y;
   if (tiles <= 0) return QSP_OK;
   dim3 grid((unsigned)std::min<long>(tiles, d->num_sms));   // persistent: one CTA per SM
+  if (mode != DEC_FP32) {
+    if (mode == DEC_FAST && !jac)
+      k_decoder_tc<TC_FAST, false><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(d->tc, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
+    else if (!jac)
+      k_decoder_tc<TC_SPLIT, false><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(d->tc, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
+    else
+      k_decoder_tc<TC_SPLIT, true><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(d->tc, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
+    LAUNCHED();
+    CK(cudaGetLastError());
+    return QSP_OK;
+  }
   if (jac)
     k_decoder_ffma<true><<<grid, FF_THREADS, FF_SMEM_BYTES, st>>>(d->dw, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
   else
@@ -211,7 +308,8 @@ extern "C" int qsp_decode_sdf(qsp_decoder* d, const float* codes, int32_t n_code
   }
   CK(cudaEventRecord(d->ev0, st));
   // grid.y is limited to 65535 codes per launch; the callers stay far below that
-  int r = launch_decoder(d, false, dp, nullptr, dc, 64, n, nullptr, n_codes, dout, nullptr, st);
+  const int mode = (flags & QSP_FLAG_FP32_CORES) ? DEC_FP32 : (flags & QSP_FLAG_FAST_FP16) ? DEC_FAST : DEC_SPLIT;
+  int r = launch_decoder(d, mode, false, dp, nullptr, dc, 64, n, nullptr, n_codes, dout, nullptr, st);
   if (r) return r;
   CK(cudaEventRecord(d->ev1, st));
   if (flags & QSP_FLAG_HOST_PTRS) {
@@ -242,7 +340,7 @@ extern "C" int qsp_decode_sdf_jacobian(qsp_decoder* d, const float* code, const 
     dc = c; dp = p;
   }
   CK(cudaEventRecord(d->ev0, st));
-  int r = launch_decoder(d, true, dp, nullptr, dc, 64, n, nullptr, 1, ds, dj, st);
+  int r = launch_decoder(d, (flags & QSP_FLAG_FP32_CORES) ? DEC_FP32 : DEC_SPLIT, true, dp, nullptr, dc, 64, n, nullptr, 1, ds, dj, st);
   if (r) return r;
   CK(cudaEventRecord(d->ev1, st));
   if (flags & QSP_FLAG_HOST_PTRS) {
@@ -385,6 +483,7 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
   GnParamsDev p{prm->k1, prm->k2, prm->k3, prm->k4, prm->b1, prm->b2, prm->lr, prm->s_damp, prm->cut_off,
                 prm->num_iterations, S};
   const int tb = 256;
+  const int hp_mode = d->precision == QSP_PREC_FP32_CORES ? DEC_FP32 : DEC_SPLIT;
   k_fill_obj_map<<<B, 128, 0, st>>>(d_rays_off, B, ray_obj); LAUNCHED();
   k_fill_obj_map<<<B, 128, 0, st>>>(d_pts_off, B, pt_obj); LAUNCHED();
   k_init_state<<<(B + 63) / 64, 64, 0, st>>>(state, in.T, in.codes, B); LAUNCHED();
@@ -399,7 +498,7 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
     k_exclusive_scan<<<1, 1024, 0, st>>>(ray_cnt, ray_base, R, counters + 0, 0, nullptr); LAUNCHED();
     k_sample<true><<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, R, S, nullptr, ray_base, q_pts, q_code); LAUNCHED();
     // (a) forward decode of the in-ball samples (loss.py:77-78)
-    if ((r = launch_decoder(d, false, q_pts, q_code, codes_dev, code_stride, 0, counters + 0, 1, q_sdf, nullptr, st))) return r;
+    if ((r = launch_decoder(d, hp_mode, false, q_pts, q_code, codes_dev, code_stride, 0, counters + 0, 1, q_sdf, nullptr, st))) return r;
     // (b) occupancy, transmittance, rendered depth, band selection
     k_render<<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, d_rays_off, in.depth, d_depth_off, R, S, p.th,
                                         ray_base, q_sdf, slot, ray_res, band_cnt); LAUNCHED();
@@ -408,7 +507,7 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
                                            row_fac, row_res, row_ray, row_samp); LAUNCHED();
     k_surface_xform<<<(M + tb - 1) / tb, tb, 0, st>>>(state, in.pts, pt_obj, M, jp_pts, jp_code); LAUNCHED();
     // (a) SDF + input Jacobian of surface and band points (loss.py:34,144)
-    if ((r = launch_decoder(d, true, jp_pts, jp_code, codes_dev, code_stride, 0, counters + 2, 1, g_sdf, g_jac, st))) return r;
+    if ((r = launch_decoder(d, hp_mode, true, jp_pts, jp_code, codes_dev, code_stride, 0, counters + 2, 1, g_sdf, g_jac, st))) return r;
     // (c) chain rule + normal equations, (d) solve + update
     k_accumulate<<<dim3(nchunk, B, 2), 256, 0, st>>>(state, d_pts_off, d_rays_off, band_base, M, jp_pts, g_sdf, g_jac,
                                                      row_fac, row_res, p.b2, p.b1, 0, nullptr, partials); LAUNCHED();
@@ -522,7 +621,7 @@ extern "C" int qsp_estimate_pose_batch(qsp_decoder* d, int32_t num_iterations, i
   const float* codes_dev = reinterpret_cast<const float*>(state) + offsetof(ObjState, code) / 4;
   for (int it = 0; it < num_iterations; ++it) {
     k_surface_xform<<<(M + tb - 1) / tb, tb, 0, st>>>(state, in.pts, pt_obj, M, jp_pts, jp_code); LAUNCHED();
-    if ((r = launch_decoder(d, true, jp_pts, jp_code, codes_dev, sizeof(ObjState) / 4, M, nullptr, 1, g_sdf, g_jac, st))) return r;
+    if ((r = launch_decoder(d, d->precision == QSP_PREC_FP32_CORES ? DEC_FP32 : DEC_SPLIT, true, jp_pts, jp_code, codes_dev, sizeof(ObjState) / 4, M, nullptr, 1, g_sdf, g_jac, st))) return r;
     k_accumulate<<<dim3(nchunk, B, 1), 256, 0, st>>>(state, d_pts_off, d_pts_off, nullptr, M, jp_pts, g_sdf, g_jac,
                                                      nullptr, nullptr, 0.f, 0.f, 1, row_active, partials); LAUNCHED();
     k_solve<<<B, 128, 0, st>>>(state, d_pts_off, nchunk, partials, p, 1, m_active, nullptr, nullptr, nullptr); LAUNCHED();

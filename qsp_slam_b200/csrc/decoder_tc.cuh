@@ -1,0 +1,360 @@
+// Kernel (a) on the 5th-generation tensor cores: fused DeepSDF decoder forward (+ reverse sweep for
+// the input Jacobian) as tcgen05.mma tiles with TMEM accumulators.  Reference:
+// deep_sdf/deep_sdf_decoder.py:75-110, reconstruct/loss_utils.py:51-103.
+//
+// One CTA per SM, persistent over row tiles.  Per layer the CTA computes D[128 x 512] = A'[128 x K] W^T:
+//   A' (activations) lives in shared memory as fp16, K-major SWIZZLE_128B, 8 K-blocks of [128][64];
+//   W streams from L2 as pre-swizzled [256 n][64 k] fp16 images (32 KB, one cp.async.bulk each) through
+//   a 3-stage mbarrier ring; D (fp32) fills all 512 TMEM columns; the epilogue warps read D back with
+//   tcgen05.ld, apply bias / ReLU / skip concat (forward) or the ReLU mask (reverse), and rewrite A'.
+//
+// Two arithmetic modes (template MODE):
+//   TC_FAST  : 128 points per tile, operands rounded to fp16 once (error ~3e-4 on the SDF): used only
+//              to classify ray samples far from the +-th band.
+//   TC_SPLIT : 64 points per tile, every operand carried as an fp16 pair (hi, lo) with x = hi + lo to
+//              ~2^-22: rows 2i / 2i+1 of A' hold hi / lo of point i, the weight stream alternates
+//              W_hi, W_lo tiles and all four partial products accumulate in fp32 in TMEM; the epilogue
+//              adds the two rows of a point.  This is fp32-equivalent arithmetic on the tensor pipe.
+//
+// Warp roles (320 threads): warp 0 = weight producer (bulk copies), warp 1 = MMA issuer + TMEM
+// owner, warps 2..9 = epilogue (TMEM lane quadrant = warp % 4, column half = (warp - 2) / 4).
+#pragma once
+#include <cuda_fp16.h>
+#include "common.cuh"
+#include "tc_common.cuh"
+
+#define TC_FAST 0
+#define TC_SPLIT 1
+#define TC_THREADS 320
+#define TC_STAGES 3
+#define TC_TILE_BYTES 32768                       // one [256][64] fp16 weight image
+#define TC_ABLK_BYTES 16384                       // one [128][64] fp16 activation K-block
+#define TC_SMEM_BYTES (8 * TC_ABLK_BYTES + TC_STAGES * TC_TILE_BYTES + 1024 + 2048)
+#define TC_SA 16.0f                               // activation scale (split mode): keeps lo parts normal in fp16
+#define TC_SW 16.0f                               // weight scale (split mode)
+#define TC_SG 256.0f                              // gradient scale of the reverse sweep (split mode)
+
+struct TcDecoderDev {
+  const uint8_t* img_fast;                        // forward weight images, fp16(W), consumption order
+  const uint8_t* img_split;                       // forward then reverse images, (hi, lo) interleaved per tile
+  const float* bias;                              // [8][512] fp32, zero padded
+  const float* w8;                                // [512] fp32
+  float b8;
+};
+
+__device__ __forceinline__ uint32_t pack_h2(float a, float b) {
+  __half2 h = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+// x -> (hi, lo) fp16 pair, two values at a time
+__device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
+  __half2 h = __floats2half2_rn(a, b);
+  float2 hf = __half22float2(h);
+  __half2 l = __floats2half2_rn(a - hf.x, b - hf.y);
+  hi = *reinterpret_cast<uint32_t*>(&h);
+  lo = *reinterpret_cast<uint32_t*>(&l);
+}
+
+// steps: 0..7 forward layers, 8..15 reverse sweep through layers 7..0
+__device__ __forceinline__ int tc_step_kblocks(int s) { return s == 0 ? 2 : 8; }
+__device__ __forceinline__ int tc_step_halves(int s) { return s == 15 ? 1 : 2; }
+
+template <int MODE, bool JAC>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restrict__ code_idx,
+             const float* __restrict__ codes, int code_stride, int n_codes, long n_host,
+             const int* __restrict__ n_dev, float* __restrict__ sdf_out, float* __restrict__ jac_out) {
+  static_assert(!(JAC && MODE == TC_FAST), "the reverse sweep exists only in split mode");
+  constexpr int ROWS = MODE == TC_SPLIT ? 64 : 128;      // points per tile
+  constexpr int TPB = MODE == TC_SPLIT ? 2 : 1;          // weight tiles per (half, k-block)
+  constexpr int NSTEPS = JAC ? 16 : 8;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;                                    // 8 x 16 KB
+  uint8_t* sB = smem + 8 * TC_ABLK_BYTES;                // TC_STAGES x 32 KB
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + TC_STAGES * TC_TILE_BYTES);
+  uint64_t* full = bars;                                 // [TC_STAGES] weights landed
+  uint64_t* empty = bars + TC_STAGES;                    // [TC_STAGES] weights consumed
+  uint64_t* act_full = bars + 2 * TC_STAGES;             // A' written by the epilogue
+  uint64_t* acc_full = bars + 2 * TC_STAGES + 1;         // D complete in TMEM
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TC_STAGES + 2);
+  float* part = reinterpret_cast<float*>(bars + 2 * TC_STAGES + 4);   // [2][128] lin8 partial sums
+
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const long n = n_dev ? (long)(*n_dev) : n_host;
+  const long ntiles = (n + ROWS - 1) / ROWS;
+  const long total_tiles = ntiles * n_codes;
+
+  if (tid == 0) {
+    for (int i = 0; i < TC_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
+    mbar_init(act_full, 256);
+    mbar_init(acc_full, 1);
+    fence_mbar_init();
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  if (warp == 0) {
+    // ================= weight producer =================
+    if (lane == 0) {
+      int stage = 0; uint32_t ph = 0;
+      const uint8_t* base = MODE == TC_SPLIT ? dw.img_split : dw.img_fast;
+      for (long gt = blockIdx.x; gt < total_tiles; gt += gridDim.x) {
+        const uint8_t* src = base;
+        for (int s = 0; s < NSTEPS; ++s) {
+          const int nt = tc_step_halves(s) * tc_step_kblocks(s) * TPB;
+          for (int t = 0; t < nt; ++t) {
+            mbar_wait(&empty[stage], ph ^ 1);
+            mbar_expect_tx(&full[stage], TC_TILE_BYTES);
+            bulk_g2s(sB + stage * TC_TILE_BYTES, src, TC_TILE_BYTES, &full[stage]);
+            src += TC_TILE_BYTES;
+            if (++stage == TC_STAGES) { stage = 0; ph ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================= MMA issuer =================
+    int stage = 0; uint32_t ph = 0, act_ph = 0;
+    const uint32_t idesc = make_idesc_f16(128, 256);
+    for (long gt = blockIdx.x; gt < total_tiles; gt += gridDim.x) {
+      for (int s = 0; s < NSTEPS; ++s) {
+        mbar_wait(act_full, act_ph); act_ph ^= 1;
+        tc_fence_after();
+        const int nh = tc_step_halves(s), nkb = tc_step_kblocks(s);
+        for (int h = 0; h < nh; ++h)
+          for (int kb = 0; kb < nkb; ++kb)
+            for (int t = 0; t < TPB; ++t) {
+              mbar_wait(&full[stage], ph);
+              tc_fence_after();
+              if (elect_one()) {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  uint64_t da = make_sdesc_sw128(sA + kb * TC_ABLK_BYTES + k * 32);
+                  uint64_t db = make_sdesc_sw128(sB + stage * TC_TILE_BYTES + k * 32);
+                  umma_f16(tmem + h * 256, da, db, idesc, (kb | t | k) != 0);
+                }
+                umma_commit(&empty[stage]);
+              }
+              __syncwarp();
+              if (++stage == TC_STAGES) { stage = 0; ph ^= 1; }
+            }
+        if (elect_one()) umma_commit(acc_full);
+        __syncwarp();
+      }
+    }
+  } else {
+    // ================= epilogue warps =================
+    const int e = tid - 64;                              // 0..255
+    const int q = warp & 3;                              // TMEM lane quadrant this warp may read
+    const int ch = (warp - 2) >> 2;                      // column half: 0 -> 0..255, 1 -> 256..511
+    const int arow = q * 32 + lane;                      // A' row == TMEM lane
+    const int pl = MODE == TC_SPLIT ? (arow >> 1) : arow;      // local point
+    const bool odd = MODE == TC_SPLIT && (lane & 1);
+    const int row_hi = MODE == TC_SPLIT ? (arow & ~1) : arow, row_lo = row_hi + 1;
+    constexpr int CW = MODE == TC_SPLIT ? 16 : 32;       // columns this thread owns per 32-column chunk
+    uint32_t acc_ph = 0;
+    uint32_t mask[8][4];
+
+    for (long gt = blockIdx.x; gt < total_tiles; gt += gridDim.x) {
+      const long cy = gt / ntiles, tile = gt - cy * ntiles;
+      const float* pass_code = codes + (size_t)cy * code_stride;
+      float* sdf_o = sdf_out ? sdf_out + (size_t)cy * n : nullptr;
+      // ---- stage the input rows [code, xyz, 0...] into K-blocks 0,1 (loss_utils.py:71-72) ----
+      {
+        constexpr int TPP = 256 / ROWS;                  // threads per point: 4 (split) or 2 (fast)
+        constexpr int COLS = 128 / TPP;                  // 32 or 64 columns each
+        const int ip = e / TPP, part_id = e % TPP;
+        const long r = tile * ROWS + ip;
+        const bool ok = r < n;
+        const float* cz = (code_idx && ok) ? codes + (size_t)code_idx[r] * code_stride : pass_code;
+#pragma unroll
+        for (int c8 = 0; c8 < COLS / 8; ++c8) {
+          const int col = part_id * COLS + c8 * 8;
+          float v[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            int c = col + j;
+            v[j] = !ok ? 0.f : c < QSP_CODE ? cz[c] : c < QSP_IN ? pts[r * 3 + (c - QSP_CODE)] : 0.f;
+          }
+          const int kb = col >> 6, c16 = (col & 63) >> 3;
+          if (MODE == TC_SPLIT) {
+            uint32_t hi[4], lo[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) split2(v[2 * j] * TC_SA, v[2 * j + 1] * TC_SA, hi[j], lo[j]);
+            *reinterpret_cast<uint4*>(sA + kb * TC_ABLK_BYTES + sw128_offset(2 * ip, c16)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+            *reinterpret_cast<uint4*>(sA + kb * TC_ABLK_BYTES + sw128_offset(2 * ip + 1, c16)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+          } else {
+            *reinterpret_cast<uint4*>(sA + kb * TC_ABLK_BYTES + sw128_offset(ip, c16)) =
+                make_uint4(pack_h2(v[0], v[1]), pack_h2(v[2], v[3]), pack_h2(v[4], v[5]), pack_h2(v[6], v[7]));
+          }
+        }
+        fence_proxy_async();
+        mbar_arrive(act_full);
+      }
+      const long grow = tile * ROWS + pl;                // global row of this thread's point
+      const bool valid = grow < n;
+      const float* my_code = (code_idx && valid) ? codes + (size_t)code_idx[grow] * code_stride : pass_code;
+      float sdf_v = 0.f;
+
+      for (int s = 0; s < NSTEPS; ++s) {
+        mbar_wait(acc_full, acc_ph); acc_ph ^= 1;
+        tc_fence_after();
+        const bool fwd = s < 8;
+        const int l = fwd ? s : 15 - s;
+        const bool active = !(s == 15 && ch == 1);       // the last reverse step only produces 256 columns
+        if (s == 15) asm volatile("bar.sync 1, 256;" ::: "memory");   // skip-gradient writes of step 11 are read below
+        float psum = 0.f;
+        uint32_t mbits[4] = {0u, 0u, 0u, 0u};
+        if (active) {
+#pragma unroll 1
+          for (int cc = 0; cc < 8; ++cc) {
+            const int col0 = ch * 256 + cc * 32;
+            uint32_t v[32];
+            tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + col0, v);
+            tmem_ld_wait();
+            float f[CW];
+            int colb;
+            if (MODE == TC_SPLIT) {                      // add the hi-row and lo-row accumulators of a point
+#pragma unroll
+              for (int j = 0; j < 16; ++j) {
+                float keep = odd ? __uint_as_float(v[16 + j]) : __uint_as_float(v[j]);
+                float send = odd ? __uint_as_float(v[j]) : __uint_as_float(v[16 + j]);
+                f[j] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+              }
+              colb = col0 + (odd ? 16 : 0);
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+              colb = col0;
+            }
+            // ---- per-column math ----
+            if (fwd) {
+              const float inv = MODE == TC_SPLIT ? 1.f / (TC_SA * TC_SW) : 1.f;
+#pragma unroll
+              for (int j4 = 0; j4 < CW / 4; ++j4) {
+                const float4 bv = __ldg(reinterpret_cast<const float4*>(dw.bias + l * QSP_HID + colb + j4 * 4));
+                const float bb[4] = {bv.x, bv.y, bv.z, bv.w};
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                  const int j = j4 * 4 + u;
+                  float x = fmaf(f[j], inv, bb[u]);                       // deep_sdf_decoder.py:91
+                  if (JAC && x > 0.f) mbits[(cc * CW + j) >> 5] |= 1u << ((cc * CW + j) & 31);
+                  x = fmaxf(x, 0.f);                                      // :103
+                  if (l == 3 && colb + j >= QSP_SKIP_COL) {               // :87-88 concat [h3, code, xyz]
+                    const int c = colb + j - QSP_SKIP_COL;
+                    x = !valid ? 0.f : c < QSP_CODE ? my_code[c] : pts[grow * 3 + (c - QSP_CODE)];
+                  }
+                  f[j] = x;
+                }
+              }
+              if (l == 7) {                                               // lin8: 512 -> 1
+#pragma unroll
+                for (int j4 = 0; j4 < CW / 4; ++j4) {
+                  const float4 wv = __ldg(reinterpret_cast<const float4*>(dw.w8 + colb + j4 * 4));
+                  psum = fmaf(f[j4 * 4 + 0], wv.x, psum); psum = fmaf(f[j4 * 4 + 1], wv.y, psum);
+                  psum = fmaf(f[j4 * 4 + 2], wv.z, psum); psum = fmaf(f[j4 * 4 + 3], wv.w, psum);
+                }
+              }
+            } else {
+              // reverse sweep: acc = SG*SW * dX.  Keep SG*dX for the next layer, mask by lin(l-1)'s ReLU.
+              const float inv = l > 0 ? 1.f / TC_SW : 1.f / (TC_SW * TC_SG);
+#pragma unroll
+              for (int j = 0; j < CW; ++j) {
+                float x = f[j] * inv;
+                const int c = colb + j;
+                if (l == 0) {
+                  if (valid && c < QSP_JSTRIDE)
+                    jac_out[(size_t)grow * QSP_JSTRIDE + c] = c < QSP_IN ? x + jac_out[(size_t)grow * QSP_JSTRIDE + c] : 0.f;
+                } else {
+                  bool keep = (mask[l - 1][(cc * CW + j) >> 5] >> ((cc * CW + j) & 31)) & 1u;
+                  if (l == 4 && c >= QSP_SKIP_COL) {                      // gradient of the re-concatenated input
+                    if (valid) jac_out[(size_t)grow * QSP_JSTRIDE + (c - QSP_SKIP_COL)] = x * (1.f / TC_SG);
+                    keep = false;
+                  }
+                  f[j] = keep ? x : 0.f;
+                }
+              }
+            }
+            // ---- rewrite A' (not after the very last step of a pass) ----
+            if (!(fwd && l == 7) && !(!fwd && l == 0)) {
+              const int kb = colb >> 6, c16 = (colb & 63) >> 3;
+              if (MODE == TC_SPLIT) {
+                const float sc = fwd ? TC_SA : 1.f;
+                uint32_t hi[8], lo[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) split2(f[2 * j] * sc, f[2 * j + 1] * sc, hi[j], lo[j]);
+                uint8_t* blk = sA + kb * TC_ABLK_BYTES;
+                *reinterpret_cast<uint4*>(blk + sw128_offset(row_hi, c16)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+                *reinterpret_cast<uint4*>(blk + sw128_offset(row_hi, c16 + 1)) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+                *reinterpret_cast<uint4*>(blk + sw128_offset(row_lo, c16)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+                *reinterpret_cast<uint4*>(blk + sw128_offset(row_lo, c16 + 1)) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+              } else {
+                uint8_t* blk = sA + kb * TC_ABLK_BYTES;
+#pragma unroll
+                for (int g = 0; g < 4; ++g)
+                  *reinterpret_cast<uint4*>(blk + sw128_offset(arow, c16 + g)) =
+                      make_uint4(pack_h2(f[8 * g], f[8 * g + 1]), pack_h2(f[8 * g + 2], f[8 * g + 3]),
+                                 pack_h2(f[8 * g + 4], f[8 * g + 5]), pack_h2(f[8 * g + 6], f[8 * g + 7]));
+              }
+            }
+          }
+        }
+        if (JAC && fwd) {
+#pragma unroll
+          for (int u = 0; u < 4; ++u) mask[l][u] = mbits[u];
+        }
+        if (fwd && l == 7) {
+          // ---- tanh head (deep_sdf_decoder.py:107-108): combine the partial dot products ----
+          if (MODE == TC_SPLIT) psum += __shfl_xor_sync(0xffffffffu, psum, 1);
+          if (MODE != TC_SPLIT || !odd) part[ch * 128 + pl] = psum;
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+          sdf_v = tanhf(part[pl] + part[128 + pl] + dw.b8);
+          if (ch == 0 && (MODE != TC_SPLIT || !odd) && valid && sdf_o) sdf_o[grow] = sdf_v;
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+          if (JAC) {
+            // seed of the reverse sweep: SG * (1 - s^2) * w8, masked by lin7's ReLU (loss_utils.py:100-101)
+            const float d = (1.f - sdf_v * sdf_v) * TC_SG;
+#pragma unroll 1
+            for (int cc = 0; cc < 8; ++cc) {
+              const int colb = ch * 256 + cc * 32 + (odd ? 16 : 0);
+              float g[16];
+#pragma unroll
+              for (int j4 = 0; j4 < 4; ++j4) {
+                const float4 wv = __ldg(reinterpret_cast<const float4*>(dw.w8 + colb + j4 * 4));
+                const float ww[4] = {wv.x, wv.y, wv.z, wv.w};
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                  const int j = j4 * 4 + u;
+                  const bool keep = (mask[7][(cc * 16 + j) >> 5] >> ((cc * 16 + j) & 31)) & 1u;
+                  g[j] = keep ? d * ww[u] : 0.f;
+                }
+              }
+              uint32_t hi[8], lo[8];
+#pragma unroll
+              for (int j = 0; j < 8; ++j) split2(g[2 * j], g[2 * j + 1], hi[j], lo[j]);
+              const int kb = colb >> 6, c16 = (colb & 63) >> 3;
+              uint8_t* blk = sA + kb * TC_ABLK_BYTES;
+              *reinterpret_cast<uint4*>(blk + sw128_offset(row_hi, c16)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+              *reinterpret_cast<uint4*>(blk + sw128_offset(row_hi, c16 + 1)) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+              *reinterpret_cast<uint4*>(blk + sw128_offset(row_lo, c16)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+              *reinterpret_cast<uint4*>(blk + sw128_offset(row_lo, c16 + 1)) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+            }
+          }
+        }
+        tc_fence_before();
+        if (s + 1 < NSTEPS) {
+          fence_proxy_async();
+          mbar_arrive(act_full);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem, 512);
+}

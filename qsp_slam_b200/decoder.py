@@ -80,8 +80,14 @@ class DeviceDecoder:
         return self
 
     # --- kernel (a) -------------------------------------------------------------------------------
-    def decode_sdf(self, codes, pts) -> np.ndarray:
-        """codes (C,64) or (64,), pts (n,3) host arrays -> (C,n) or (n,) float32  (loss_utils.py:51-79)."""
+    def set_precision(self, precision: str):
+        """Arithmetic of the decoder inside the GN loop: "tensor" (tcgen05, fp16-pair operands, default)
+        or "fp32" (exact-fp32 CUDA-core kernel, for validation)."""
+        N.check(N.lib().qsp_set_precision(self.handle, {"tensor": N.PREC_TENSOR, "fp32": N.PREC_FP32_CORES}[precision]))
+
+    def decode_sdf(self, codes, pts, mode: str = "tensor") -> np.ndarray:
+        """codes (C,64) or (64,), pts (n,3) host arrays -> (C,n) or (n,) float32  (loss_utils.py:51-79).
+        mode: "tensor" (fp16-pair tensor-core kernel), "fast" (single-pass fp16), "fp32" (CUDA cores)."""
         codes = N.f32(codes)
         single = codes.ndim == 1
         codes = codes.reshape(-1, 64)
@@ -90,18 +96,18 @@ class DeviceDecoder:
         out = np.empty((codes.shape[0], pts.shape[0]), np.float32)
         if pts.shape[0]:
             N.check(N.lib().qsp_decode_sdf(self.handle, N.ptr(codes), codes.shape[0], N.ptr(pts), pts.shape[0],
-                                           N.ptr(out), N.FLAG_HOST_PTRS, None))
+                                           N.ptr(out), N.FLAG_HOST_PTRS | N.MODE_FLAGS[mode], None))
         return out[0] if single else out
 
-    def decode_sdf_device(self, codes, pts, out, sync: bool = True):
+    def decode_sdf_device(self, codes, pts, out, sync: bool = True, mode: str = "tensor"):
         """Same with torch CUDA tensors (float32, contiguous); ``out`` (C,n) is written in place."""
         n_codes = codes.numel() // 64
         n = pts.shape[0]
         N.check(N.lib().qsp_decode_sdf(self.handle, N.ptr(codes), n_codes, N.ptr(pts), n, N.ptr(out),
-                                       N.FLAG_SYNC if sync else 0, None))
+                                       (N.FLAG_SYNC if sync else 0) | N.MODE_FLAGS[mode], None))
         return out
 
-    def decode_sdf_jacobian(self, code, pts):
+    def decode_sdf_jacobian(self, code, pts, mode: str = "tensor"):
         """(sdf (n,), d sdf/d[code,xyz] (n,67)) - loss_utils.py:82-103."""
         code = N.f32(code).reshape(64)
         pts = np.ascontiguousarray(N.f32(pts)[:, :3])
@@ -110,12 +116,12 @@ class DeviceDecoder:
         jac = np.empty((n, N.JAC_STRIDE), np.float32)
         if n:
             N.check(N.lib().qsp_decode_sdf_jacobian(self.handle, N.ptr(code), N.ptr(pts), n, N.ptr(sdf), N.ptr(jac),
-                                                    N.FLAG_HOST_PTRS, None))
+                                                    N.FLAG_HOST_PTRS | N.MODE_FLAGS[mode], None))
         return sdf, jac[:, :67]
 
-    def decode_sdf_jacobian_device(self, code, pts, sdf, jac, sync: bool = True):
+    def decode_sdf_jacobian_device(self, code, pts, sdf, jac, sync: bool = True, mode: str = "tensor"):
         N.check(N.lib().qsp_decode_sdf_jacobian(self.handle, N.ptr(code), N.ptr(pts), pts.shape[0], N.ptr(sdf),
-                                                N.ptr(jac), N.FLAG_SYNC if sync else 0, None))
+                                                N.ptr(jac), (N.FLAG_SYNC if sync else 0) | N.MODE_FLAGS[mode], None))
 
     def last_kernel_ms(self) -> float:
         ms = C.c_float()
