@@ -34,7 +34,8 @@ struct Buf {
 struct IterDebug {
   std::vector<float> H, b, dx;         // (B,71,71), (B,71), (B,71)
   std::vector<int> counts;             // (B,4)
-  std::vector<int> band_off, row_ray, row_samp;
+  std::vector<int> band_off, row_ray, row_samp;   // candidate rows (ray-major)
+  std::vector<float> row_fac;                     // de_ds of the row; 0 = not a kept band point
 };
 
 struct qsp_decoder {
@@ -48,7 +49,7 @@ struct qsp_decoder {
   Buf in_T, in_code, in_pts, in_rays, in_depth, in_scale, out_rec;
   Buf pts_off, rays_off, depth_off, ray_obj, pt_obj;
   Buf state, counters, ray_cnt, ray_base, band_cnt, band_base;
-  Buf q_pts, q_code, q_sdf, slot, ray_res;
+  Buf q_pts, q_code, q_samp, cand_q, q_sdf, slot, ray_res;
   Buf jp_pts, jp_code, g_sdf, g_jac, row_fac, row_res, row_ray, row_samp, row_active, m_active;
   Buf partials, dbgH, dbgb, dbgdx;
   Buf dec_pts, dec_codes, dec_out, dec_jac;
@@ -235,7 +236,7 @@ extern "C" void qsp_decoder_destroy(qsp_decoder* d) {
   for (void* p : d->weight_allocs) cudaFree(p);
   Buf* bufs[] = {&d->in_T, &d->in_code, &d->in_pts, &d->in_rays, &d->in_depth, &d->in_scale, &d->out_rec,
                  &d->pts_off, &d->rays_off, &d->depth_off, &d->ray_obj, &d->pt_obj, &d->state, &d->counters,
-                 &d->ray_cnt, &d->ray_base, &d->band_cnt, &d->band_base, &d->q_pts, &d->q_code, &d->q_sdf,
+                 &d->ray_cnt, &d->ray_base, &d->band_cnt, &d->band_base, &d->q_pts, &d->q_code, &d->q_samp, &d->cand_q, &d->q_sdf,
                  &d->slot, &d->ray_res, &d->jp_pts, &d->jp_code, &d->g_sdf, &d->g_jac, &d->row_fac,
                  &d->row_res, &d->row_ray, &d->row_samp, &d->row_active, &d->m_active, &d->partials,
                  &d->dbgH, &d->dbgb, &d->dbgdx, &d->dec_pts, &d->dec_codes, &d->dec_out, &d->dec_jac};
@@ -445,7 +446,7 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
 
   ObjState* state; int *counters, *ray_obj, *pt_obj, *ray_cnt, *ray_base, *band_cnt, *band_base;
   float *q_pts, *q_sdf, *slot, *ray_res, *jp_pts, *g_sdf, *g_jac, *row_fac, *row_res, *partials, *d_rec;
-  int *q_code, *jp_code, *row_ray, *row_samp;
+  int *q_code, *q_samp, *cand_q, *jp_code, *row_ray, *row_samp;
   ENSURE(d->state, B, state);
   ENSURE(d->counters, 8, counters);
   ENSURE(d->ray_obj, R, ray_obj);
@@ -456,6 +457,8 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
   ENSURE(d->band_base, R + 1, band_base);
   ENSURE(d->q_pts, qcap * 3, q_pts);
   ENSURE(d->q_code, qcap, q_code);
+  ENSURE(d->q_samp, qcap, q_samp);
+  ENSURE(d->cand_q, bandcap, cand_q);
   ENSURE(d->q_sdf, qcap, q_sdf);
   ENSURE(d->slot, qcap, slot);
   ENSURE(d->ray_res, R, ray_res);
@@ -491,23 +494,34 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
   const float* codes_dev = reinterpret_cast<const float*>(state) + offsetof(ObjState, code) / 4;
   const int code_stride = sizeof(ObjState) / 4;
 
+  // first pass over the ray samples: single-pass fp16 tensor kernel + margin, or the exact kernel
+  const int first_mode = d->precision == QSP_PREC_FP32_CORES ? DEC_FP32 : DEC_FAST;
+  const float cand_lim = p.th + (first_mode == DEC_FAST ? QSP_FAST_MARGIN : 0.f);
+  const int cand_blocks = (int)((bandcap + tb - 1) / tb);
+  CK(cudaMemsetAsync(counters, 0, 8 * sizeof(int), st));
   for (int it = 0; it < prm->num_iterations; ++it) {
     k_prep<<<(B + 63) / 64, 64, 0, st>>>(state, B, S); LAUNCHED();
     // (b) sample, in-ball test, ordered compaction
-    k_sample<false><<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, R, S, ray_cnt, nullptr, nullptr, nullptr); LAUNCHED();
+    k_sample<false><<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, R, S, ray_cnt, nullptr, nullptr, nullptr, nullptr); LAUNCHED();
     k_exclusive_scan<<<1, 1024, 0, st>>>(ray_cnt, ray_base, R, counters + 0, 0, nullptr); LAUNCHED();
-    k_sample<true><<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, R, S, nullptr, ray_base, q_pts, q_code); LAUNCHED();
-    // (a) forward decode of the in-ball samples (loss.py:77-78)
-    if ((r = launch_decoder(d, hp_mode, false, q_pts, q_code, codes_dev, code_stride, 0, counters + 0, 1, q_sdf, nullptr, st))) return r;
+    k_sample<true><<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, R, S, nullptr, ray_base, q_pts, q_code, q_samp); LAUNCHED();
+    // (a) forward decode of the in-ball samples (loss.py:77-78), first pass
+    if ((r = launch_decoder(d, first_mode, false, q_pts, q_code, codes_dev, code_stride, 0, counters + 0, 1, q_sdf, nullptr, st))) return r;
+    // candidates near the band, appended behind the surface points in the Jacobian row list
+    k_candidates<false><<<ray_blocks, tb, 0, st>>>(ray_base, R, q_sdf, cand_lim, band_cnt, nullptr, M, (int)bandcap, nullptr,
+                                                   nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr); LAUNCHED();
+    k_exclusive_scan<<<1, 1024, 0, st>>>(band_cnt, band_base, R, counters + 1, M, counters + 2); LAUNCHED();
+    k_candidates<true><<<ray_blocks, tb, 0, st>>>(ray_base, R, q_sdf, cand_lim, nullptr, band_base, M, (int)bandcap, q_pts,
+                                                  q_code, q_samp, jp_pts, jp_code, row_ray, row_samp, cand_q, counters + 3); LAUNCHED();
+    k_surface_xform<<<(M + tb - 1) / tb, tb, 0, st>>>(state, in.pts, pt_obj, M, jp_pts, jp_code); LAUNCHED();
+    // (a) SDF + input Jacobian of surface points and candidates (loss.py:34,144), fp32-equivalent
+    if ((r = launch_decoder(d, hp_mode, true, jp_pts, jp_code, codes_dev, code_stride, 0, counters + 2, 1, g_sdf, g_jac, st))) return r;
+    k_refine_scatter<<<cand_blocks, tb, 0, st>>>(counters + 1, (int)bandcap, cand_q, g_sdf, M, q_sdf); LAUNCHED();
     // (b) occupancy, transmittance, rendered depth, band selection
     k_render<<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, d_rays_off, in.depth, d_depth_off, R, S, p.th,
-                                        ray_base, q_sdf, slot, ray_res, band_cnt); LAUNCHED();
-    k_exclusive_scan<<<1, 1024, 0, st>>>(band_cnt, band_base, R, counters + 1, M, counters + 2); LAUNCHED();
-    k_band_fill<<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, R, S, slot, ray_res, band_base, M, jp_pts, jp_code,
-                                           row_fac, row_res, row_ray, row_samp); LAUNCHED();
-    k_surface_xform<<<(M + tb - 1) / tb, tb, 0, st>>>(state, in.pts, pt_obj, M, jp_pts, jp_code); LAUNCHED();
-    // (a) SDF + input Jacobian of surface and band points (loss.py:34,144)
-    if ((r = launch_decoder(d, hp_mode, true, jp_pts, jp_code, codes_dev, code_stride, 0, counters + 2, 1, g_sdf, g_jac, st))) return r;
+                                        ray_base, q_sdf, slot, ray_res, ray_cnt); LAUNCHED();
+    k_row_factors<<<cand_blocks, tb, 0, st>>>(counters + 1, (int)bandcap, M, S, row_ray, row_samp, slot, ray_res,
+                                              row_fac, row_res); LAUNCHED();
     // (c) chain rule + normal equations, (d) solve + update
     k_accumulate<<<dim3(nchunk, B, 2), 256, 0, st>>>(state, d_pts_off, d_rays_off, band_base, M, jp_pts, g_sdf, g_jac,
                                                      row_fac, row_res, p.b2, p.b1, 0, nullptr, partials); LAUNCHED();
@@ -529,10 +543,11 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
         g.counts[o * 4 + 2] = hs[o].n_keep; g.counts[o * 4 + 3] = hs[o].failed;
       }
       int P = std::min<int>(g.band_off[R], (int)bandcap);
-      g.row_ray.resize(P); g.row_samp.resize(P);
+      g.row_ray.resize(P); g.row_samp.resize(P); g.row_fac.resize(P);
       if (P > 0) {
         CK(cudaMemcpy(g.row_ray.data(), row_ray + M, (size_t)P * 4, cudaMemcpyDeviceToHost));
         CK(cudaMemcpy(g.row_samp.data(), row_samp + M, (size_t)P * 4, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(g.row_fac.data(), row_fac + M, (size_t)P * 4, cudaMemcpyDeviceToHost));
       }
       d->dbg.push_back(std::move(g));
     }
@@ -544,6 +559,11 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
     CK(cudaStreamSynchronize(st));
   } else if (flags & QSP_FLAG_SYNC) {
     CK(cudaStreamSynchronize(st));
+  }
+  if (host || (flags & QSP_FLAG_SYNC)) {
+    int ovf = 0;
+    CK(cudaMemcpy(&ovf, counters + 3, sizeof(int), cudaMemcpyDeviceToHost));
+    if (ovf) { g_err = "candidate row capacity exceeded"; return QSP_ERR_ALLOC; }
   }
   return QSP_OK;
 }
@@ -567,10 +587,14 @@ extern "C" int qsp_get_band_indices(qsp_decoder* d, int32_t it, int32_t b, int32
   if (b < 0 || b + 1 >= (int)d->h_rays_off.size()) { g_err = "no such object"; return QSP_ERR_INVALID; }
   int r0 = d->h_rays_off[b], r1 = d->h_rays_off[b + 1];
   int lo = g.band_off[r0], hi = std::min<int>(g.band_off[r1], (int)g.row_ray.size());
-  int n = std::max(0, hi - lo);
-  for (int i = 0; i < n && i < cap; ++i) {
-    if (ray) ray[i] = g.row_ray[lo + i] - r0;
-    if (sample) sample[i] = g.row_samp[lo + i];
+  int n = 0;
+  for (int i = lo; i < hi; ++i) {
+    if (g.row_fac[i] == 0.f) continue;               // candidate that is not a kept band point
+    if (n < cap) {
+      if (ray) ray[n] = g.row_ray[i] - r0;
+      if (sample) sample[n] = g.row_samp[i];
+    }
+    ++n;
   }
   return n;
 }

@@ -10,6 +10,7 @@
 #define QSP_JSTRIDE 68
 #define QSP_NDOF_ 71
 #define QSP_NTRI 2556             // 71*72/2 upper-triangle entries of J^T J
+#define QSP_FAST_MARGIN 0.006f    // candidate band = th + margin; the single-pass fp16 SDF error stays below ~2e-3
 #define QSP_PART_STRIDE 2640      // 2556 (H) + 71 (b) + 1 (sum of robust residual^2) padded to a multiple of 16
 
 // Folded decoder weights on the device (fp32 copies for the exact FFMA path).

@@ -128,7 +128,8 @@ __device__ __forceinline__ RayCtx load_ray(const ObjState* st, int o, const floa
 template <bool FILL>
 __global__ void k_sample(const ObjState* __restrict__ st, const float* __restrict__ rays,
                          const int* __restrict__ ray_obj, int R, int S, int* __restrict__ ray_cnt,
-                         const int* __restrict__ ray_base, float* __restrict__ q_pts, int* __restrict__ q_code) {
+                         const int* __restrict__ ray_base, float* __restrict__ q_pts, int* __restrict__ q_code,
+                         int* __restrict__ q_samp) {
   int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (r >= R) return;
   int o = ray_obj[r];
@@ -151,6 +152,7 @@ __global__ void k_sample(const ObjState* __restrict__ st, const float* __restric
       int idx = base + cnt + __popc(m & ((1u << lane) - 1u));
       q_pts[idx * 3 + 0] = x; q_pts[idx * 3 + 1] = y; q_pts[idx * 3 + 2] = z;
       q_code[idx] = o;
+      q_samp[idx] = j;
     }
     cnt += __popc(m);
   }
@@ -410,6 +412,7 @@ k_accumulate(const ObjState* __restrict__ st, const int* __restrict__ pts_off,
       else if (c == 71) {
         float r = term == 0 ? g_sdf[row] : row_res[row];
         val = pose_only ? r : huber_weight(r, term == 0 ? b_sdf : b_render) * r;
+        if (term == 1 && fac == 0.f) val = 0.f;          // candidate row that is not a kept band point
         if (row_active) val *= row_active[row];
       } else {
         float g0 = fac * g[64], g1 = fac * g[65], g2 = fac * g[66];
@@ -638,4 +641,67 @@ __global__ void k_finalize_pose_only(const ObjState* __restrict__ st, const floa
   for (int r = 0; r < 3; ++r)
     for (int c = 0; c < 3; ++c) T[r * 4 + c] /= scale[o];
   for (int i = 0; i < 16; ++i) out[o * 16 + i] = T[i];
+}
+
+// ------------------------------------------------------------------------------------------------
+// candidate rows: in-ball samples whose first-pass SDF lies within +-lim of zero (lim = th + margin
+// when the first pass is the single-pass fp16 kernel, lim = th when it is exact).  They are
+// re-evaluated, with the input Jacobian, by the fp32-equivalent kernel; every true band point
+// (loss.py:88) is among them as long as the first-pass error stays below the margin.
+// Order: (ray, sample) ascending, i.e. the order torch.where gives (loss.py:68,89-90).
+// ------------------------------------------------------------------------------------------------
+template <bool FILL>
+__global__ void k_candidates(const int* __restrict__ ray_base, int R, const float* __restrict__ q_sdf,
+                             float lim, int* __restrict__ cand_cnt, const int* __restrict__ cand_base,
+                             int row0, int cap, const float* __restrict__ q_pts, const int* __restrict__ q_code,
+                             const int* __restrict__ q_samp, float* __restrict__ jp_pts, int* __restrict__ jp_code,
+                             int* __restrict__ row_ray, int* __restrict__ row_samp, int* __restrict__ cand_q,
+                             int* __restrict__ overflow) {
+  int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (r >= R) return;
+  const int lo = ray_base[r], hi = ray_base[r + 1];
+  int cnt = 0;
+  const int base = FILL ? cand_base[r] : 0;
+  for (int i0 = lo; i0 < hi; i0 += 32) {
+    int i = i0 + lane;
+    bool c = false;
+    if (i < hi) { float s = q_sdf[i]; c = (s > -lim) && (s < lim); }
+    unsigned m = __ballot_sync(0xffffffffu, c);
+    if (FILL && c) {
+      int k = base + cnt + __popc(m & ((1u << lane) - 1u));
+      if (k < cap) {
+        int row = row0 + k;
+        jp_pts[row * 3] = q_pts[i * 3]; jp_pts[row * 3 + 1] = q_pts[i * 3 + 1]; jp_pts[row * 3 + 2] = q_pts[i * 3 + 2];
+        jp_code[row] = q_code[i];
+        row_ray[row] = r;
+        row_samp[row] = q_samp[i];
+        cand_q[k] = i;
+      } else {
+        *overflow = 1;
+      }
+    }
+    cnt += __popc(m);
+  }
+  if (!FILL && lane == 0) cand_cnt[r] = cnt;
+}
+
+// exact SDF of the candidates back into the per-sample list read by k_render
+__global__ void k_refine_scatter(const int* __restrict__ n_cand, int cap, const int* __restrict__ cand_q,
+                                 const float* __restrict__ g_sdf, int row0, float* __restrict__ q_sdf) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= min(*n_cand, cap)) return;
+  q_sdf[cand_q[k]] = g_sdf[row0 + k];
+}
+
+// per candidate row: de_ds of its (ray, sample) slot (0 when it is not a kept band point) and the
+// ray's clamped depth residual
+__global__ void k_row_factors(const int* __restrict__ n_cand, int cap, int row0, int S,
+                              const int* __restrict__ row_ray, const int* __restrict__ row_samp,
+                              const float* __restrict__ slot_de_ds, const float* __restrict__ ray_res,
+                              float* __restrict__ row_fac, float* __restrict__ row_res) {
+  int k = blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= min(*n_cand, cap)) return;
+  int row = row0 + k, r = row_ray[row];
+  row_fac[row] = slot_de_ds[(size_t)r * S + row_samp[row]];
+  row_res[row] = ray_res[r];
 }
