@@ -29,7 +29,7 @@
 #define TC_STAGES 3
 #define TC_TILE_BYTES 32768                       // one [256][64] fp16 weight image
 #define TC_ABLK_BYTES 16384                       // one [128][64] fp16 activation K-block
-#define TC_SMEM_BYTES (8 * TC_ABLK_BYTES + TC_STAGES * TC_TILE_BYTES + 1024 + 2048)
+#define TC_SMEM_BYTES (8 * TC_ABLK_BYTES + TC_STAGES * TC_TILE_BYTES + 256 + 2048)
 #define TC_SA 16.0f                               // activation scale (split mode): keeps lo parts normal in fp16
 #define TC_SW 16.0f                               // weight scale (split mode)
 #define TC_SG 256.0f                              // gradient scale of the reverse sweep (split mode)
@@ -59,6 +59,15 @@ __device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t&
 __device__ __forceinline__ int tc_step_kblocks(int s) { return s == 0 ? 2 : 8; }
 __device__ __forceinline__ int tc_step_halves(int s) { return s == 15 ? 1 : 2; }
 
+// Barrier protocol (every barrier completes exactly once per step; a role waits for completion #it
+// with parity it & 1, for completion #(it-1) with the opposite parity):
+//   full/empty[stage]  weight ring (producer <-> MMA)
+//   a_ready[kb]        A' K-block kb holds the operands of step it      (128 epilogue arrivals)
+//   a_free[kb]         the MMAs of step it no longer read K-block kb     (tcgen05.commit)
+//   acc_full[h]        accumulator half h (256 TMEM columns) of step it is complete (tcgen05.commit)
+//   acc_free[h]        the epilogue has read accumulator half h of step it (256 arrivals)
+// This lets the epilogue of half 0 run under the MMAs of half 1, and the epilogue of half 1 under the
+// MMAs of the next layer's half 0: the tensor pipe only waits for K-blocks that are not yet rewritten.
 template <int MODE, bool JAC>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restrict__ code_idx,
@@ -69,17 +78,20 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
   constexpr int TPB = MODE == TC_SPLIT ? 2 : 1;          // weight tiles per (half, k-block)
   constexpr int NSTEPS = JAC ? 16 : 8;
 
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = smem_raw;                              // checked below: must be 1024-byte aligned
   uint8_t* sA = smem;                                    // 8 x 16 KB
   uint8_t* sB = smem + 8 * TC_ABLK_BYTES;                // TC_STAGES x 32 KB
   uint64_t* bars = reinterpret_cast<uint64_t*>(sB + TC_STAGES * TC_TILE_BYTES);
-  uint64_t* full = bars;                                 // [TC_STAGES] weights landed
-  uint64_t* empty = bars + TC_STAGES;                    // [TC_STAGES] weights consumed
-  uint64_t* act_full = bars + 2 * TC_STAGES;             // A' written by the epilogue
-  uint64_t* acc_full = bars + 2 * TC_STAGES + 1;         // D complete in TMEM
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * TC_STAGES + 2);
-  float* part = reinterpret_cast<float*>(bars + 2 * TC_STAGES + 4);   // [2][128] lin8 partial sums
+  uint64_t* full = bars;                                 // [3]
+  uint64_t* empty = bars + 3;                            // [3]
+  uint64_t* acc_full = bars + 6;                         // [2]
+  uint64_t* acc_free = bars + 8;                         // [2]
+  uint64_t* a_ready = bars + 10;                         // [8]
+  uint64_t* a_free = bars + 18;                          // [8]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 26);
+  float* sbias = reinterpret_cast<float*>(bars + 32);    // [512] bias of the current layer
+  float* part = sbias;                                   // [2][128] lin8 partial sums (aliases sbias)
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const long n = n_dev ? (long)(*n_dev) : n_host;
@@ -87,9 +99,10 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
   const long total_tiles = ntiles * n_codes;
 
   if (tid == 0) {
+    if (smem_u32(smem) & 1023) asm volatile("trap;");
     for (int i = 0; i < TC_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    mbar_init(act_full, 256);
-    mbar_init(acc_full, 1);
+    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_free[i], 256); }
+    for (int i = 0; i < 8; ++i) { mbar_init(&a_ready[i], 128); mbar_init(&a_free[i], 1); }
     fence_mbar_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, 512);
@@ -119,190 +132,225 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
     }
   } else if (warp == 1) {
     // ================= MMA issuer =================
-    int stage = 0; uint32_t ph = 0, act_ph = 0;
+    int stage = 0; uint32_t ph = 0, it = 0;
     const uint32_t idesc = make_idesc_f16(128, 256);
     for (long gt = blockIdx.x; gt < total_tiles; gt += gridDim.x) {
-      for (int s = 0; s < NSTEPS; ++s) {
-        mbar_wait(act_full, act_ph); act_ph ^= 1;
-        tc_fence_after();
+      for (int s = 0; s < NSTEPS; ++s, ++it) {
+        const uint32_t par = it & 1;
         const int nh = tc_step_halves(s), nkb = tc_step_kblocks(s);
-        for (int h = 0; h < nh; ++h)
-          for (int kb = 0; kb < nkb; ++kb)
-            for (int t = 0; t < TPB; ++t) {
-              mbar_wait(&full[stage], ph);
-              tc_fence_after();
-              if (elect_one()) {
+        for (int h = 0; h < 2; ++h) {
+          mbar_wait(&acc_free[h], par ^ 1);              // previous step's epilogue has drained this half
+          tc_fence_after();
+          if (h < nh) {
+            for (int kb = 0; kb < nkb; ++kb) {
+              if (h == 0) { mbar_wait(&a_ready[kb], par); tc_fence_after(); }
+              for (int t = 0; t < TPB; ++t) {
+                mbar_wait(&full[stage], ph);
+                tc_fence_after();
+                if (elect_one()) {
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                  uint64_t da = make_sdesc_sw128(sA + kb * TC_ABLK_BYTES + k * 32);
-                  uint64_t db = make_sdesc_sw128(sB + stage * TC_TILE_BYTES + k * 32);
-                  umma_f16(tmem + h * 256, da, db, idesc, (kb | t | k) != 0);
+                  for (int k = 0; k < 4; ++k) {
+                    uint64_t da = make_sdesc_sw128(sA + kb * TC_ABLK_BYTES + k * 32);
+                    uint64_t db = make_sdesc_sw128(sB + stage * TC_TILE_BYTES + k * 32);
+                    umma_f16(tmem + h * 256, da, db, idesc, (kb | t | k) != 0);
+                  }
+                  umma_commit(&empty[stage]);
+                  if (h == nh - 1 && t == TPB - 1) umma_commit(&a_free[kb]);
                 }
-                umma_commit(&empty[stage]);
+                __syncwarp();
+                if (++stage == TC_STAGES) { stage = 0; ph ^= 1; }
               }
-              __syncwarp();
-              if (++stage == TC_STAGES) { stage = 0; ph ^= 1; }
             }
-        if (elect_one()) umma_commit(acc_full);
-        __syncwarp();
+          }
+          if (elect_one()) {
+            umma_commit(&acc_full[h]);
+            if (h == 1) for (int kb = nkb; kb < 8; ++kb) umma_commit(&a_free[kb]);
+          }
+          __syncwarp();
+        }
       }
     }
   } else {
     // ================= epilogue warps =================
     const int e = tid - 64;                              // 0..255
     const int q = warp & 3;                              // TMEM lane quadrant this warp may read
-    const int ch = (warp - 2) >> 2;                      // column half: 0 -> 0..255, 1 -> 256..511
+    const int g = (warp - 2) >> 2;                       // column group: 128 of the 256 columns of a half
     const int arow = q * 32 + lane;                      // A' row == TMEM lane
     const int pl = MODE == TC_SPLIT ? (arow >> 1) : arow;      // local point
     const bool odd = MODE == TC_SPLIT && (lane & 1);
     const int row_hi = MODE == TC_SPLIT ? (arow & ~1) : arow, row_lo = row_hi + 1;
     constexpr int CW = MODE == TC_SPLIT ? 16 : 32;       // columns this thread owns per 32-column chunk
-    uint32_t acc_ph = 0;
+    uint32_t it = 0;
     uint32_t mask[8][4];
+
+    // writes CW consecutive activations (columns colb..) of this thread's row(s) into A'
+    auto store_cols = [&](const float* f, int colb, float sc) {
+      uint8_t* blk = sA + (colb >> 6) * TC_ABLK_BYTES;
+      const int c16 = (colb & 63) >> 3;
+      if (MODE == TC_SPLIT) {
+        uint32_t hi[8], lo[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) split2(f[2 * j] * sc, f[2 * j + 1] * sc, hi[j], lo[j]);
+        *reinterpret_cast<uint4*>(blk + sw128_offset(row_hi, c16)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(blk + sw128_offset(row_hi, c16 + 1)) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
+        *reinterpret_cast<uint4*>(blk + sw128_offset(row_lo, c16)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        *reinterpret_cast<uint4*>(blk + sw128_offset(row_lo, c16 + 1)) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+      } else {
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          *reinterpret_cast<uint4*>(blk + sw128_offset(arow, c16 + u)) =
+              make_uint4(pack_h2(f[8 * u], f[8 * u + 1]), pack_h2(f[8 * u + 2], f[8 * u + 3]),
+                         pack_h2(f[8 * u + 4], f[8 * u + 5]), pack_h2(f[8 * u + 6], f[8 * u + 7]));
+      }
+    };
 
     for (long gt = blockIdx.x; gt < total_tiles; gt += gridDim.x) {
       const long cy = gt / ntiles, tile = gt - cy * ntiles;
       const float* pass_code = codes + (size_t)cy * code_stride;
       float* sdf_o = sdf_out ? sdf_out + (size_t)cy * n : nullptr;
-      // ---- stage the input rows [code, xyz, 0...] into K-blocks 0,1 (loss_utils.py:71-72) ----
-      {
-        constexpr int TPP = 256 / ROWS;                  // threads per point: 4 (split) or 2 (fast)
-        constexpr int COLS = 128 / TPP;                  // 32 or 64 columns each
-        const int ip = e / TPP, part_id = e % TPP;
-        const long r = tile * ROWS + ip;
-        const bool ok = r < n;
-        const float* cz = (code_idx && ok) ? codes + (size_t)code_idx[r] * code_stride : pass_code;
-#pragma unroll
-        for (int c8 = 0; c8 < COLS / 8; ++c8) {
-          const int col = part_id * COLS + c8 * 8;
-          float v[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            int c = col + j;
-            v[j] = !ok ? 0.f : c < QSP_CODE ? cz[c] : c < QSP_IN ? pts[r * 3 + (c - QSP_CODE)] : 0.f;
-          }
-          const int kb = col >> 6, c16 = (col & 63) >> 3;
-          if (MODE == TC_SPLIT) {
-            uint32_t hi[4], lo[4];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) split2(v[2 * j] * TC_SA, v[2 * j + 1] * TC_SA, hi[j], lo[j]);
-            *reinterpret_cast<uint4*>(sA + kb * TC_ABLK_BYTES + sw128_offset(2 * ip, c16)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-            *reinterpret_cast<uint4*>(sA + kb * TC_ABLK_BYTES + sw128_offset(2 * ip + 1, c16)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-          } else {
-            *reinterpret_cast<uint4*>(sA + kb * TC_ABLK_BYTES + sw128_offset(ip, c16)) =
-                make_uint4(pack_h2(v[0], v[1]), pack_h2(v[2], v[3]), pack_h2(v[4], v[5]), pack_h2(v[6], v[7]));
-          }
-        }
-        fence_proxy_async();
-        mbar_arrive(act_full);
-      }
       const long grow = tile * ROWS + pl;                // global row of this thread's point
       const bool valid = grow < n;
       const float* my_code = (code_idx && valid) ? codes + (size_t)code_idx[grow] * code_stride : pass_code;
+      // ---- stage the input rows [code, xyz, 0...] into K-blocks 0,1 (loss_utils.py:71-72) ----
+      // group g owns K-blocks {2g, 2g+1, 4+2g, 4+2g+1}; group 0 writes K-blocks 0 and 1 here.
+      {
+        const uint32_t prev = (it & 1) ^ 1;              // the previous step's MMAs released the K-blocks
+#pragma unroll
+        for (int u = 0; u < 4; ++u) mbar_wait(&a_free[(u >> 1) * 4 + 2 * g + (u & 1)], prev);
+        if (g == 0) {
+          const int rr = e;                              // A' row 0..127
+          const int ip = MODE == TC_SPLIT ? (rr >> 1) : rr;
+          const long r = tile * ROWS + ip;
+          const bool ok = r < n;
+          const float* cz = (code_idx && ok) ? codes + (size_t)code_idx[r] * code_stride : pass_code;
+#pragma unroll 1
+          for (int c8 = 0; c8 < 16; ++c8) {
+            const int col = c8 * 8;
+            uint32_t w[4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              float v2[2];
+#pragma unroll
+              for (int u = 0; u < 2; ++u) {
+                const int c = col + 2 * j + u;
+                v2[u] = !ok ? 0.f : c < QSP_CODE ? cz[c] : c < QSP_IN ? pts[r * 3 + (c - QSP_CODE)] : 0.f;
+              }
+              if (MODE == TC_SPLIT) {
+                uint32_t hi, lo;
+                split2(v2[0] * TC_SA, v2[1] * TC_SA, hi, lo);
+                w[j] = (rr & 1) ? lo : hi;
+              } else {
+                w[j] = pack_h2(v2[0], v2[1]);
+              }
+            }
+            *reinterpret_cast<uint4*>(sA + (col >> 6) * TC_ABLK_BYTES + sw128_offset(rr, (col & 63) >> 3)) =
+                make_uint4(w[0], w[1], w[2], w[3]);
+          }
+          fence_proxy_async();
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) mbar_arrive(&a_ready[(u >> 1) * 4 + 2 * g + (u & 1)]);
+      }
       float sdf_v = 0.f;
 
-      for (int s = 0; s < NSTEPS; ++s) {
-        mbar_wait(acc_full, acc_ph); acc_ph ^= 1;
-        tc_fence_after();
+      for (int s = 0; s < NSTEPS; ++s, ++it) {
+        const uint32_t par = it & 1;
         const bool fwd = s < 8;
         const int l = fwd ? s : 15 - s;
-        const bool active = !(s == 15 && ch == 1);       // the last reverse step only produces 256 columns
+        const int nh = tc_step_halves(s);
+        const bool last = s + 1 == NSTEPS;
+        const bool rewrite = !(fwd && l == 7) && !last;
+        if (fwd) {                                       // bias of this layer -> smem (all epilogue threads)
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+          *reinterpret_cast<float2*>(sbias + 2 * e) = __ldg(reinterpret_cast<const float2*>(dw.bias + l * QSP_HID + 2 * e));
+          asm volatile("bar.sync 1, 256;" ::: "memory");
+        }
         if (s == 15) asm volatile("bar.sync 1, 256;" ::: "memory");   // skip-gradient writes of step 11 are read below
         float psum = 0.f;
         uint32_t mbits[4] = {0u, 0u, 0u, 0u};
-        if (active) {
+        for (int h = 0; h < 2; ++h) {
+          mbar_wait(&acc_full[h], par);
+          tc_fence_after();
+          if (h < nh) {
 #pragma unroll 1
-          for (int cc = 0; cc < 8; ++cc) {
-            const int col0 = ch * 256 + cc * 32;
-            uint32_t v[32];
-            tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + col0, v);
-            tmem_ld_wait();
-            float f[CW];
-            int colb;
-            if (MODE == TC_SPLIT) {                      // add the hi-row and lo-row accumulators of a point
+            for (int cc = 0; cc < 4; ++cc) {
+              const int col0 = h * 256 + g * 128 + cc * 32;
+              const int kb = col0 >> 6;
+              const int bit0 = (h * 4 + cc) * CW;
+              uint32_t v[32];
+              tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + col0, v);
+              tmem_ld_wait();
+              float f[CW];
+              int colb;
+              if (MODE == TC_SPLIT) {                    // add the hi-row and lo-row accumulators of a point
 #pragma unroll
-              for (int j = 0; j < 16; ++j) {
-                float keep = odd ? __uint_as_float(v[16 + j]) : __uint_as_float(v[j]);
-                float send = odd ? __uint_as_float(v[j]) : __uint_as_float(v[16 + j]);
-                f[j] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
-              }
-              colb = col0 + (odd ? 16 : 0);
-            } else {
-#pragma unroll
-              for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
-              colb = col0;
-            }
-            // ---- per-column math ----
-            if (fwd) {
-              const float inv = MODE == TC_SPLIT ? 1.f / (TC_SA * TC_SW) : 1.f;
-#pragma unroll
-              for (int j4 = 0; j4 < CW / 4; ++j4) {
-                const float4 bv = __ldg(reinterpret_cast<const float4*>(dw.bias + l * QSP_HID + colb + j4 * 4));
-                const float bb[4] = {bv.x, bv.y, bv.z, bv.w};
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                  const int j = j4 * 4 + u;
-                  float x = fmaf(f[j], inv, bb[u]);                       // deep_sdf_decoder.py:91
-                  if (JAC && x > 0.f) mbits[(cc * CW + j) >> 5] |= 1u << ((cc * CW + j) & 31);
-                  x = fmaxf(x, 0.f);                                      // :103
-                  if (l == 3 && colb + j >= QSP_SKIP_COL) {               // :87-88 concat [h3, code, xyz]
-                    const int c = colb + j - QSP_SKIP_COL;
-                    x = !valid ? 0.f : c < QSP_CODE ? my_code[c] : pts[grow * 3 + (c - QSP_CODE)];
-                  }
-                  f[j] = x;
+                for (int j = 0; j < 16; ++j) {
+                  float keep = odd ? __uint_as_float(v[16 + j]) : __uint_as_float(v[j]);
+                  float send = odd ? __uint_as_float(v[j]) : __uint_as_float(v[16 + j]);
+                  f[j] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
                 }
+                colb = col0 + (odd ? 16 : 0);
+              } else {
+#pragma unroll
+                for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+                colb = col0;
               }
-              if (l == 7) {                                               // lin8: 512 -> 1
+              if (fwd) {
+                const float inv = MODE == TC_SPLIT ? 1.f / (TC_SA * TC_SW) : 1.f;
 #pragma unroll
                 for (int j4 = 0; j4 < CW / 4; ++j4) {
-                  const float4 wv = __ldg(reinterpret_cast<const float4*>(dw.w8 + colb + j4 * 4));
-                  psum = fmaf(f[j4 * 4 + 0], wv.x, psum); psum = fmaf(f[j4 * 4 + 1], wv.y, psum);
-                  psum = fmaf(f[j4 * 4 + 2], wv.z, psum); psum = fmaf(f[j4 * 4 + 3], wv.w, psum);
-                }
-              }
-            } else {
-              // reverse sweep: acc = SG*SW * dX.  Keep SG*dX for the next layer, mask by lin(l-1)'s ReLU.
-              const float inv = l > 0 ? 1.f / TC_SW : 1.f / (TC_SW * TC_SG);
+                  const float4 bv = *reinterpret_cast<const float4*>(sbias + colb + j4 * 4);
+                  const float bb[4] = {bv.x, bv.y, bv.z, bv.w};
 #pragma unroll
-              for (int j = 0; j < CW; ++j) {
-                float x = f[j] * inv;
-                const int c = colb + j;
-                if (l == 0) {
-                  if (valid && c < QSP_JSTRIDE)
-                    jac_out[(size_t)grow * QSP_JSTRIDE + c] = c < QSP_IN ? x + jac_out[(size_t)grow * QSP_JSTRIDE + c] : 0.f;
-                } else {
-                  bool keep = (mask[l - 1][(cc * CW + j) >> 5] >> ((cc * CW + j) & 31)) & 1u;
-                  if (l == 4 && c >= QSP_SKIP_COL) {                      // gradient of the re-concatenated input
-                    if (valid) jac_out[(size_t)grow * QSP_JSTRIDE + (c - QSP_SKIP_COL)] = x * (1.f / TC_SG);
-                    keep = false;
+                  for (int u = 0; u < 4; ++u) {
+                    const int j = j4 * 4 + u;
+                    float x = fmaf(f[j], inv, bb[u]);                       // deep_sdf_decoder.py:91
+                    if (JAC && x > 0.f) mbits[(bit0 + j) >> 5] |= 1u << ((bit0 + j) & 31);
+                    x = fmaxf(x, 0.f);                                      // :103
+                    if (l == 3 && colb + j >= QSP_SKIP_COL) {               // :87-88 concat [h3, code, xyz]
+                      const int c = colb + j - QSP_SKIP_COL;
+                      x = !valid ? 0.f : c < QSP_CODE ? my_code[c] : pts[grow * 3 + (c - QSP_CODE)];
+                    }
+                    f[j] = x;
                   }
-                  f[j] = keep ? x : 0.f;
+                }
+                if (l == 7) {                                               // lin8: 512 -> 1
+#pragma unroll
+                  for (int j4 = 0; j4 < CW / 4; ++j4) {
+                    const float4 wv = __ldg(reinterpret_cast<const float4*>(dw.w8 + colb + j4 * 4));
+                    psum = fmaf(f[j4 * 4 + 0], wv.x, psum); psum = fmaf(f[j4 * 4 + 1], wv.y, psum);
+                    psum = fmaf(f[j4 * 4 + 2], wv.z, psum); psum = fmaf(f[j4 * 4 + 3], wv.w, psum);
+                  }
+                }
+              } else {
+                // reverse sweep: acc = SG*SW * dX.  Keep SG*dX for the next layer, mask by lin(l-1)'s ReLU.
+                const float inv = l > 0 ? 1.f / TC_SW : 1.f / (TC_SW * TC_SG);
+#pragma unroll
+                for (int j = 0; j < CW; ++j) {
+                  float x = f[j] * inv;
+                  const int c = colb + j;
+                  if (l == 0) {
+                    if (valid && c < QSP_JSTRIDE)
+                      jac_out[(size_t)grow * QSP_JSTRIDE + c] = c < QSP_IN ? x + jac_out[(size_t)grow * QSP_JSTRIDE + c] : 0.f;
+                  } else {
+                    bool keep = (mask[l - 1][(bit0 + j) >> 5] >> ((bit0 + j) & 31)) & 1u;
+                    if (l == 4 && c >= QSP_SKIP_COL) {                      // gradient of the re-concatenated input
+                      if (valid) jac_out[(size_t)grow * QSP_JSTRIDE + (c - QSP_SKIP_COL)] = x * (1.f / TC_SG);
+                      keep = false;
+                    }
+                    f[j] = keep ? x : 0.f;
+                  }
                 }
               }
-            }
-            // ---- rewrite A' (not after the very last step of a pass) ----
-            if (!(fwd && l == 7) && !(!fwd && l == 0)) {
-              const int kb = colb >> 6, c16 = (colb & 63) >> 3;
-              if (MODE == TC_SPLIT) {
-                const float sc = fwd ? TC_SA : 1.f;
-                uint32_t hi[8], lo[8];
-#pragma unroll
-                for (int j = 0; j < 8; ++j) split2(f[2 * j] * sc, f[2 * j + 1] * sc, hi[j], lo[j]);
-                uint8_t* blk = sA + kb * TC_ABLK_BYTES;
-                *reinterpret_cast<uint4*>(blk + sw128_offset(row_hi, c16)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-                *reinterpret_cast<uint4*>(blk + sw128_offset(row_hi, c16 + 1)) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
-                *reinterpret_cast<uint4*>(blk + sw128_offset(row_lo, c16)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-                *reinterpret_cast<uint4*>(blk + sw128_offset(row_lo, c16 + 1)) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
-              } else {
-                uint8_t* blk = sA + kb * TC_ABLK_BYTES;
-#pragma unroll
-                for (int g = 0; g < 4; ++g)
-                  *reinterpret_cast<uint4*>(blk + sw128_offset(arow, c16 + g)) =
-                      make_uint4(pack_h2(f[8 * g], f[8 * g + 1]), pack_h2(f[8 * g + 2], f[8 * g + 3]),
-                                 pack_h2(f[8 * g + 4], f[8 * g + 5]), pack_h2(f[8 * g + 6], f[8 * g + 7]));
+              if (rewrite) {
+                if ((cc & 1) == 0) mbar_wait(&a_free[kb], par);   // this step's MMAs are done with K-block kb
+                store_cols(f, colb, (MODE == TC_SPLIT && fwd) ? TC_SA : 1.f);
+                if (cc & 1) { fence_proxy_async(); mbar_arrive(&a_ready[kb]); }
               }
             }
           }
+          tc_fence_before();
+          mbar_arrive(&acc_free[h]);
         }
         if (JAC && fwd) {
 #pragma unroll
@@ -311,18 +359,20 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
         if (fwd && l == 7) {
           // ---- tanh head (deep_sdf_decoder.py:107-108): combine the partial dot products ----
           if (MODE == TC_SPLIT) psum += __shfl_xor_sync(0xffffffffu, psum, 1);
-          if (MODE != TC_SPLIT || !odd) part[ch * 128 + pl] = psum;
+          asm volatile("bar.sync 1, 256;" ::: "memory");             // everybody is done with sbias
+          if (MODE != TC_SPLIT || !odd) part[g * 128 + pl] = psum;
           asm volatile("bar.sync 1, 256;" ::: "memory");
           sdf_v = tanhf(part[pl] + part[128 + pl] + dw.b8);
-          if (ch == 0 && (MODE != TC_SPLIT || !odd) && valid && sdf_o) sdf_o[grow] = sdf_v;
-          asm volatile("bar.sync 1, 256;" ::: "memory");
+          if (g == 0 && (MODE != TC_SPLIT || !odd) && valid && sdf_o) sdf_o[grow] = sdf_v;
           if (JAC) {
             // seed of the reverse sweep: SG * (1 - s^2) * w8, masked by lin7's ReLU (loss_utils.py:100-101)
             const float d = (1.f - sdf_v * sdf_v) * TC_SG;
 #pragma unroll 1
-            for (int cc = 0; cc < 8; ++cc) {
-              const int colb = ch * 256 + cc * 32 + (odd ? 16 : 0);
-              float g[16];
+            for (int c8 = 0; c8 < 8; ++c8) {
+              const int h = c8 >> 2, cc = c8 & 3;
+              const int col0 = h * 256 + g * 128 + cc * 32, kb = col0 >> 6;
+              const int colb = col0 + (odd ? 16 : 0), bit0 = (h * 4 + cc) * 16;
+              float gsd[16];
 #pragma unroll
               for (int j4 = 0; j4 < 4; ++j4) {
                 const float4 wv = __ldg(reinterpret_cast<const float4*>(dw.w8 + colb + j4 * 4));
@@ -330,26 +380,15 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                   const int j = j4 * 4 + u;
-                  const bool keep = (mask[7][(cc * 16 + j) >> 5] >> ((cc * 16 + j) & 31)) & 1u;
-                  g[j] = keep ? d * ww[u] : 0.f;
+                  const bool keep = (mask[7][(bit0 + j) >> 5] >> ((bit0 + j) & 31)) & 1u;
+                  gsd[j] = keep ? d * ww[u] : 0.f;
                 }
               }
-              uint32_t hi[8], lo[8];
-#pragma unroll
-              for (int j = 0; j < 8; ++j) split2(g[2 * j], g[2 * j + 1], hi[j], lo[j]);
-              const int kb = colb >> 6, c16 = (colb & 63) >> 3;
-              uint8_t* blk = sA + kb * TC_ABLK_BYTES;
-              *reinterpret_cast<uint4*>(blk + sw128_offset(row_hi, c16)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-              *reinterpret_cast<uint4*>(blk + sw128_offset(row_hi, c16 + 1)) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
-              *reinterpret_cast<uint4*>(blk + sw128_offset(row_lo, c16)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-              *reinterpret_cast<uint4*>(blk + sw128_offset(row_lo, c16 + 1)) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+              if ((cc & 1) == 0) mbar_wait(&a_free[kb], par);
+              store_cols(gsd, colb, 1.f);
+              if (cc & 1) { fence_proxy_async(); mbar_arrive(&a_ready[kb]); }
             }
           }
-        }
-        tc_fence_before();
-        if (s + 1 < NSTEPS) {
-          fence_proxy_async();
-          mbar_arrive(act_full);
         }
       }
     }

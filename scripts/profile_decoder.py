@@ -15,7 +15,9 @@ def ball(n):
 z = torch.zeros(64, device="cuda")
 xf, xj = ball(nf), ball(nj)
 so, sj, jo = torch.empty(nf, device="cuda"), torch.empty(nj, device="cuda"), torch.empty((nj, 68), device="cuda")
+mode_f = sys.argv[3] if len(sys.argv) > 3 else "fast"
+mode_j = sys.argv[4] if len(sys.argv) > 4 else "tensor"
 for i in range(3):
-    dev.decode_sdf_device(z, xf, so); t1 = dev.last_kernel_ms()
-    dev.decode_sdf_jacobian_device(z, xj, sj, jo); t2 = dev.last_kernel_ms()
-print(f"fwd {nf} rows {t1:.3f} ms  {nf*3.67104e6/t1/1e9:.1f} TFLOP/s ; jac {nj} rows {t2:.3f} ms {nj*7.34208e6/t2/1e9:.1f} TFLOP/s")
+    dev.decode_sdf_device(z, xf, so, mode=mode_f); t1 = dev.last_kernel_ms()
+    dev.decode_sdf_jacobian_device(z, xj, sj, jo, mode=mode_j); t2 = dev.last_kernel_ms()
+print(f"fwd[{mode_f}] {nf} rows {t1:.3f} ms  {nf*3.67104e6/t1/1e9:.1f} TFLOP/s ; jac[{mode_j}] {nj} rows {t2:.3f} ms {nj*7.34208e6/t2/1e9:.1f} TFLOP/s")
