@@ -224,6 +224,10 @@ extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_
   CK(cudaFuncSetAttribute(k_decoder_tc<TC_SPLIT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
   CK(cudaFuncSetAttribute(k_decoder_ffma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FF_SMEM_BYTES));
   CK(cudaFuncSetAttribute(k_decoder_ffma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FF_SMEM_BYTES));
+  if (const char* dbg_env = getenv("QSP_TC_DEBUG")) {
+    int v = atoi(dbg_env);
+    CK(cudaMemcpyToSymbol(g_tc_dbg, &v, sizeof(int)));
+  }
   CK(cudaEventCreate(&d->ev0));
   CK(cudaEventCreate(&d->ev1));
   *out = d;

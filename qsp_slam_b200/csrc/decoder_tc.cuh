@@ -16,8 +16,8 @@
 //              W_hi, W_lo tiles and all four partial products accumulate in fp32 in TMEM; the epilogue
 //              adds the two rows of a point.  This is fp32-equivalent arithmetic on the tensor pipe.
 //
-// Warp roles (320 threads): warp 0 = weight producer (bulk copies), warp 1 = MMA issuer + TMEM
-// owner, warps 2..9 = epilogue (TMEM lane quadrant = warp % 4, column half = (warp - 2) / 4).
+// Warp roles: warp 0 = weight producer (bulk copies), warp 1 = MMA issuer + TMEM owner, warps 2.. =
+// epilogue in TC_NG groups of 4 warps (TMEM lane quadrant = warp % 4, column group = (warp - 2) / 4).
 #pragma once
 #include <cuda_fp16.h>
 #include "common.cuh"
@@ -25,7 +25,11 @@
 
 #define TC_FAST 0
 #define TC_SPLIT 1
-#define TC_THREADS 320
+#ifndef TC_NG
+#define TC_NG 2                                   // epilogue warp groups (128 threads each)
+#endif
+#define TC_EPI (TC_NG * 128)
+#define TC_THREADS (64 + TC_EPI)
 #define TC_STAGES 3
 #define TC_TILE_BYTES 32768                       // one [256][64] fp16 weight image
 #define TC_ABLK_BYTES 16384                       // one [128][64] fp16 activation K-block
@@ -33,6 +37,10 @@
 #define TC_SA 16.0f                               // activation scale (split mode): keeps lo parts normal in fp16
 #define TC_SW 16.0f                               // weight scale (split mode)
 #define TC_SG 256.0f                              // gradient scale of the reverse sweep (split mode)
+
+// timing experiments only (QSP_TC_DEBUG env var at handle creation): bit0 = no weight copies,
+// bit1 = epilogue skips math and stores.  Results are garbage when non-zero.
+__device__ int g_tc_dbg = 0;
 
 struct TcDecoderDev {
   const uint8_t* img_fast;                        // forward weight images, fp16(W), consumption order
@@ -101,7 +109,7 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
   if (tid == 0) {
     if (smem_u32(smem) & 1023) asm volatile("trap;");
     for (int i = 0; i < TC_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_free[i], 256); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_free[i], TC_EPI); }
     for (int i = 0; i < 8; ++i) { mbar_init(&a_ready[i], 128); mbar_init(&a_free[i], 1); }
     fence_mbar_init();
   }
@@ -110,6 +118,7 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_slot;
+  const int dbg = g_tc_dbg;
 
   if (warp == 0) {
     // ================= weight producer =================
@@ -122,6 +131,7 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
           const int nt = tc_step_halves(s) * tc_step_kblocks(s) * TPB;
           for (int t = 0; t < nt; ++t) {
             mbar_wait(&empty[stage], ph ^ 1);
+            if (dbg & 1) { mbar_arrive(&full[stage]); src += TC_TILE_BYTES; if (++stage == TC_STAGES) { stage = 0; ph ^= 1; } continue; }
             mbar_expect_tx(&full[stage], TC_TILE_BYTES);
             bulk_g2s(sB + stage * TC_TILE_BYTES, src, TC_TILE_BYTES, &full[stage]);
             src += TC_TILE_BYTES;
@@ -172,9 +182,11 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
     }
   } else {
     // ================= epilogue warps =================
-    const int e = tid - 64;                              // 0..255
+    const int e = tid - 64;                              // 0..TC_EPI-1
+    constexpr int KPG = 4 / TC_NG;                       // K-blocks a group owns per accumulator half
+    constexpr int NCH = 2 * KPG;                         // 32-column chunks per thread per half
     const int q = warp & 3;                              // TMEM lane quadrant this warp may read
-    const int g = (warp - 2) >> 2;                       // column group: 128 of the 256 columns of a half
+    const int g = (warp - 2) >> 2;                       // column group: 256/TC_NG columns of each half
     const int arow = q * 32 + lane;                      // A' row == TMEM lane
     const int pl = MODE == TC_SPLIT ? (arow >> 1) : arow;      // local point
     const bool odd = MODE == TC_SPLIT && (lane & 1);
@@ -216,16 +228,16 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
       {
         const uint32_t prev = (it & 1) ^ 1;              // the previous step's MMAs released the K-blocks
 #pragma unroll
-        for (int u = 0; u < 4; ++u) mbar_wait(&a_free[(u >> 1) * 4 + 2 * g + (u & 1)], prev);
-        if (g == 0) {
-          const int rr = e;                              // A' row 0..127
+        for (int u = 0; u < 2 * KPG; ++u) mbar_wait(&a_free[(u / KPG) * 4 + KPG * g + (u % KPG)], prev);
+        if (g * KPG < 2) {                               // the groups that own K-blocks 0 and 1
+          const int rr = e & 127;                        // A' row 0..127
           const int ip = MODE == TC_SPLIT ? (rr >> 1) : rr;
           const long r = tile * ROWS + ip;
           const bool ok = r < n;
           const float* cz = (code_idx && ok) ? codes + (size_t)code_idx[r] * code_stride : pass_code;
 #pragma unroll 1
-          for (int c8 = 0; c8 < 16; ++c8) {
-            const int col = c8 * 8;
+          for (int c8 = 0; c8 < 8 * KPG; ++c8) {
+            const int col = g * KPG * 64 + c8 * 8;
             uint32_t w[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
@@ -249,7 +261,7 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
           fence_proxy_async();
         }
 #pragma unroll
-        for (int u = 0; u < 4; ++u) mbar_arrive(&a_ready[(u >> 1) * 4 + 2 * g + (u & 1)]);
+        for (int u = 0; u < 2 * KPG; ++u) mbar_arrive(&a_ready[(u / KPG) * 4 + KPG * g + (u % KPG)]);
       }
       float sdf_v = 0.f;
 
@@ -261,25 +273,44 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
         const bool last = s + 1 == NSTEPS;
         const bool rewrite = !(fwd && l == 7) && !last;
         if (fwd) {                                       // bias of this layer -> smem (all epilogue threads)
-          asm volatile("bar.sync 1, 256;" ::: "memory");
-          *reinterpret_cast<float2*>(sbias + 2 * e) = __ldg(reinterpret_cast<const float2*>(dw.bias + l * QSP_HID + 2 * e));
-          asm volatile("bar.sync 1, 256;" ::: "memory");
+          asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI) : "memory");
+          if (e < 256) *reinterpret_cast<float2*>(sbias + 2 * e) = __ldg(reinterpret_cast<const float2*>(dw.bias + l * QSP_HID + 2 * e));
+          asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI) : "memory");
         }
-        if (s == 15) asm volatile("bar.sync 1, 256;" ::: "memory");   // skip-gradient writes of step 11 are read below
+        if (s == 15) asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI) : "memory");   // skip-gradient writes of step 11 are read below
         float psum = 0.f;
         uint32_t mbits[4] = {0u, 0u, 0u, 0u};
         for (int h = 0; h < 2; ++h) {
           mbar_wait(&acc_full[h], par);
           tc_fence_after();
           if (h < nh) {
-#pragma unroll 1
-            for (int cc = 0; cc < 4; ++cc) {
-              const int col0 = h * 256 + g * 128 + cc * 32;
+            // software pipeline: the TMEM load of chunk cc+1 is in flight while chunk cc is processed
+            uint32_t vbuf[2][32];
+            const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + h * 256 + g * (NCH * 32);
+            if (!(dbg & 2)) tmem_ld32(tbase, vbuf[0]);
+#pragma unroll
+            for (int cc = 0; cc < NCH; ++cc) {
+              const int col0 = h * 256 + g * (NCH * 32) + cc * 32;
               const int kb = col0 >> 6;
-              const int bit0 = (h * 4 + cc) * CW;
-              uint32_t v[32];
-              tmem_ld32(tmem + ((uint32_t)(q * 32) << 16) + col0, v);
+              const int bit0 = (h * NCH + cc) * CW;
+              if (dbg & 2) {
+                if (rewrite) {
+                  if ((cc & 1) == 0) mbar_wait(&a_free[kb], par);
+                  if (cc & 1) { fence_proxy_async(); mbar_arrive(&a_ready[kb]); }
+                }
+                continue;
+              }
               tmem_ld_wait();
+              if (cc + 1 < NCH) tmem_ld32(tbase + (cc + 1) * 32, vbuf[(cc + 1) & 1]);
+              uint32_t (&v)[32] = vbuf[cc & 1];
+              if (dbg & 4) {                               // timing experiment: TMEM reads only
+                if (v[0] == 0x7fc12345u && v[31] == 0x7fc54321u) psum += 1.f;
+                if (rewrite) {
+                  if ((cc & 1) == 0) mbar_wait(&a_free[kb], par);
+                  if (cc & 1) { fence_proxy_async(); mbar_arrive(&a_ready[kb]); }
+                }
+                continue;
+              }
               float f[CW];
               int colb;
               if (MODE == TC_SPLIT) {                    // add the hi-row and lo-row accumulators of a point
@@ -306,12 +337,14 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
                     const int j = j4 * 4 + u;
                     float x = fmaf(f[j], inv, bb[u]);                       // deep_sdf_decoder.py:91
                     if (JAC && x > 0.f) mbits[(bit0 + j) >> 5] |= 1u << ((bit0 + j) & 31);
-                    x = fmaxf(x, 0.f);                                      // :103
-                    if (l == 3 && colb + j >= QSP_SKIP_COL) {               // :87-88 concat [h3, code, xyz]
-                      const int c = colb + j - QSP_SKIP_COL;
-                      x = !valid ? 0.f : c < QSP_CODE ? my_code[c] : pts[grow * 3 + (c - QSP_CODE)];
-                    }
-                    f[j] = x;
+                    f[j] = fmaxf(x, 0.f);                                   // :103
+                  }
+                }
+                if (l == 3 && colb + CW > QSP_SKIP_COL) {                   // :87-88 concat [h3, code, xyz]
+#pragma unroll
+                  for (int j = 0; j < CW; ++j) {
+                    const int c = colb + j - QSP_SKIP_COL;
+                    if (c >= 0) f[j] = !valid ? 0.f : c < QSP_CODE ? my_code[c] : pts[grow * 3 + (c - QSP_CODE)];
                   }
                 }
                 if (l == 7) {                                               // lin8: 512 -> 1
@@ -324,27 +357,40 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
                 }
               } else {
                 // reverse sweep: acc = SG*SW * dX.  Keep SG*dX for the next layer, mask by lin(l-1)'s ReLU.
-                const float inv = l > 0 ? 1.f / TC_SW : 1.f / (TC_SW * TC_SG);
+                if (l == 0) {                                               // d sdf / d [code, xyz]
+                  if (valid && colb < QSP_JSTRIDE) {
 #pragma unroll
-                for (int j = 0; j < CW; ++j) {
-                  float x = f[j] * inv;
-                  const int c = colb + j;
-                  if (l == 0) {
-                    if (valid && c < QSP_JSTRIDE)
-                      jac_out[(size_t)grow * QSP_JSTRIDE + c] = c < QSP_IN ? x + jac_out[(size_t)grow * QSP_JSTRIDE + c] : 0.f;
-                  } else {
-                    bool keep = (mask[l - 1][(bit0 + j) >> 5] >> ((bit0 + j) & 31)) & 1u;
-                    if (l == 4 && c >= QSP_SKIP_COL) {                      // gradient of the re-concatenated input
-                      if (valid) jac_out[(size_t)grow * QSP_JSTRIDE + (c - QSP_SKIP_COL)] = x * (1.f / TC_SG);
-                      keep = false;
+                    for (int j = 0; j < CW; ++j) {
+                      const int c = colb + j;
+                      if (c < QSP_JSTRIDE) {
+                        float* o = jac_out + (size_t)grow * QSP_JSTRIDE + c;
+                        *o = c < QSP_IN ? f[j] * (1.f / (TC_SW * TC_SG)) + *o : 0.f;
+                      }
                     }
-                    f[j] = keep ? x : 0.f;
+                  }
+                } else {
+                  if (l == 4 && colb + CW > QSP_SKIP_COL) {                 // gradient of the re-concatenated input
+#pragma unroll
+                    for (int j = 0; j < CW; ++j) {
+                      const int c = colb + j - QSP_SKIP_COL;
+                      if (c >= 0) {
+                        if (valid) jac_out[(size_t)grow * QSP_JSTRIDE + c] = f[j] * (1.f / (TC_SW * TC_SG));
+                        f[j] = 0.f;
+                      }
+                    }
+                  }
+                  const uint32_t mw0 = mask[l - 1][bit0 >> 5];              // CW consecutive mask bits (CW = 16)
+#pragma unroll
+                  for (int j = 0; j < CW; ++j) {
+                    const bool keep = (mw0 >> ((bit0 + j) & 31)) & 1u;
+                    f[j] = keep ? f[j] * (1.f / TC_SW) : 0.f;
                   }
                 }
               }
               if (rewrite) {
                 if ((cc & 1) == 0) mbar_wait(&a_free[kb], par);   // this step's MMAs are done with K-block kb
-                store_cols(f, colb, (MODE == TC_SPLIT && fwd) ? TC_SA : 1.f);
+                if (!(dbg & 8)) store_cols(f, colb, (MODE == TC_SPLIT && fwd) ? TC_SA : 1.f);
+                else if (f[0] == 123.456f) psum += f[CW - 1];
                 if (cc & 1) { fence_proxy_async(); mbar_arrive(&a_ready[kb]); }
               }
             }
@@ -359,19 +405,24 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
         if (fwd && l == 7) {
           // ---- tanh head (deep_sdf_decoder.py:107-108): combine the partial dot products ----
           if (MODE == TC_SPLIT) psum += __shfl_xor_sync(0xffffffffu, psum, 1);
-          asm volatile("bar.sync 1, 256;" ::: "memory");             // everybody is done with sbias
-          if (MODE != TC_SPLIT || !odd) part[g * 128 + pl] = psum;
-          asm volatile("bar.sync 1, 256;" ::: "memory");
-          sdf_v = tanhf(part[pl] + part[128 + pl] + dw.b8);
+          asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI) : "memory");             // everybody is done with sbias
+          if (MODE != TC_SPLIT || !odd) part[g * 128 + pl] = psum;               // [TC_NG][128]
+          asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI) : "memory");
+          {
+            float tot = dw.b8;
+#pragma unroll
+            for (int u = 0; u < TC_NG; ++u) tot += part[u * 128 + pl];
+            sdf_v = tanhf(tot);
+          }
           if (g == 0 && (MODE != TC_SPLIT || !odd) && valid && sdf_o) sdf_o[grow] = sdf_v;
           if (JAC) {
             // seed of the reverse sweep: SG * (1 - s^2) * w8, masked by lin7's ReLU (loss_utils.py:100-101)
             const float d = (1.f - sdf_v * sdf_v) * TC_SG;
 #pragma unroll 1
-            for (int c8 = 0; c8 < 8; ++c8) {
-              const int h = c8 >> 2, cc = c8 & 3;
-              const int col0 = h * 256 + g * 128 + cc * 32, kb = col0 >> 6;
-              const int colb = col0 + (odd ? 16 : 0), bit0 = (h * 4 + cc) * 16;
+            for (int c8 = 0; c8 < 2 * NCH; ++c8) {
+              const int h = c8 / NCH, cc = c8 % NCH;
+              const int col0 = h * 256 + g * (NCH * 32) + cc * 32, kb = col0 >> 6;
+              const int colb = col0 + (odd ? 16 : 0), bit0 = (h * NCH + cc) * 16;
               float gsd[16];
 #pragma unroll
               for (int j4 = 0; j4 < 4; ++j4) {

@@ -152,9 +152,11 @@ def test_full_loop_close_to_reference(golden, dev):
         out = opt.reconstruct_object(golden[p + "t_cam_obj"], golden[p + "pts"], golden[p + "rays"], golden[p + "depth"])
         assert out.is_good == bool(golden[p + "full_good"])
         t_ref = golden[p + "full_t"]
-        # chaotic loop (the reference differs from itself across thread counts): loose
+        # The loop is chaotic: fp32 and fp64 runs of the same algorithm part ways at iteration 2 and
+        # their losses wander in 0.27..0.41 (redwood0) for the next eight iterations
+        # (scripts/trajectory.py).  Tight checks are per iteration; this one is loose.
         assert np.abs(out.t_cam_obj - t_ref).max() < 3e-2 * np.abs(t_ref).max()
-        assert abs(out.loss - float(golden[p + "full_loss"])) < 0.25 * abs(float(golden[p + "full_loss"]))
+        assert 0.5 < out.loss / float(golden[p + "full_loss"]) < 2.0
         assert out.t_cam_obj.dtype == np.float32 and out.code.shape == (64,)
 
 
