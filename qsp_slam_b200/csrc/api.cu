@@ -529,7 +529,7 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
     // (c) chain rule + normal equations, (d) solve + update
     k_accumulate<<<dim3(nchunk, B, 2), 256, 0, st>>>(state, d_pts_off, d_rays_off, band_base, M, jp_pts, g_sdf, g_jac,
                                                      row_fac, row_res, p.b2, p.b1, 0, nullptr, partials); LAUNCHED();
-    k_solve<<<B, 128, 0, st>>>(state, d_pts_off, nchunk, partials, p, 0, nullptr, dbgH, dbgb, dbgdx); LAUNCHED();
+    k_solve<<<B, 256, 0, st>>>(state, d_pts_off, nchunk, partials, p, 0, nullptr, dbgH, dbgb, dbgdx); LAUNCHED();
     CK(cudaGetLastError());
     if (d->debug) {  // parity inspection: copy this iteration's normal equations and index lists out
       CK(cudaStreamSynchronize(st));
@@ -653,7 +653,7 @@ extern "C" int qsp_estimate_pose_batch(qsp_decoder* d, int32_t num_iterations, i
     if ((r = launch_decoder(d, d->precision == QSP_PREC_FP32_CORES ? DEC_FP32 : DEC_SPLIT, true, jp_pts, jp_code, codes_dev, sizeof(ObjState) / 4, M, nullptr, 1, g_sdf, g_jac, st))) return r;
     k_accumulate<<<dim3(nchunk, B, 1), 256, 0, st>>>(state, d_pts_off, d_pts_off, nullptr, M, jp_pts, g_sdf, g_jac,
                                                      nullptr, nullptr, 0.f, 0.f, 1, row_active, partials); LAUNCHED();
-    k_solve<<<B, 128, 0, st>>>(state, d_pts_off, nchunk, partials, p, 1, m_active, nullptr, nullptr, nullptr); LAUNCHED();
+    k_solve<<<B, 256, 0, st>>>(state, d_pts_off, nchunk, partials, p, 1, m_active, nullptr, nullptr, nullptr); LAUNCHED();
     if (it == 4) {  // optimizer.py:80-82
       CK(cudaMemsetAsync(m_active, 0, (size_t)B * 4, st));
       k_prune<<<(M + tb - 1) / tb, tb, 0, st>>>(g_sdf, pt_obj, M, row_active, m_active); LAUNCHED();

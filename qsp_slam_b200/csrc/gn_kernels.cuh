@@ -484,7 +484,7 @@ __device__ inline void exp_sim3_dev(const float* x, float* M, bool se3) {
 // H is SPD after damping so the solutions agree to rounding), exp map and state update (:261-263).
 // One CTA per object.  `ndof` = 71 (joint) or 6 (pose only, optimizer.py:72-78).
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(256)
 k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
         const float* __restrict__ partials, GnParamsDev p, int pose_only,
         const int* __restrict__ m_active, float* __restrict__ dbg_H, float* __restrict__ dbg_b, float* __restrict__ dbg_dx) {
@@ -499,12 +499,16 @@ k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
   const int n = pose_only ? 6 : 71;
   const float ws = pose_only ? 1.f : p.k2, wr = pose_only ? 0.f : p.k1;
   // fixed-order reduction of the chunk partials; entry e of the 72x72 upper triangle
-  for (int e = tid; e < 2628; e += 128) {
+  for (int e = tid; e < 2628; e += blockDim.x) {
     float ss = 0.f, sr = 0.f;
-    for (int c = 0; c < nchunk; ++c) {
-      ss += partials[(((size_t)o * 2 + 0) * nchunk + c) * QSP_PART_STRIDE + e];
-      if (!pose_only) sr += partials[(((size_t)o * 2 + 1) * nchunk + c) * QSP_PART_STRIDE + e];
+    float vs[16], vr[16];                               // all loads in flight first, then a fixed-order sum
+#pragma unroll
+    for (int c = 0; c < 16; ++c) {
+      vs[c] = c < nchunk ? partials[(((size_t)o * 2 + 0) * nchunk + c) * QSP_PART_STRIDE + e] : 0.f;
+      vr[c] = (c < nchunk && !pose_only) ? partials[(((size_t)o * 2 + 1) * nchunk + c) * QSP_PART_STRIDE + e] : 0.f;
     }
+#pragma unroll
+    for (int c = 0; c < 16; ++c) { ss += vs[c]; sr += vr[c]; }
     int i = 0, r = e;
     while (r >= 72 - i) { r -= 72 - i; ++i; }
     int j = i + r;
@@ -533,7 +537,7 @@ k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
     rhs[tid] = (double)b;
   }
   __syncthreads();
-  for (int v = tid; v < n * n; v += 128) {
+  for (int v = tid; v < n * n; v += blockDim.x) {
     int i = v / n, j = v - i * n;
     float h = (float)A[i][j];
     if (pose_only) { if (i == j) h += 1e-2f; }                           // optimizer.py:74
@@ -548,30 +552,30 @@ k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
   }
   if (dbg_b && tid < n) dbg_b[o * 71 + tid] = (float)rhs[tid];
   __syncthreads();
-  // in-place Cholesky A = L L^T (lower), fp64
+  // In-place Cholesky A = L L^T (lower), fp64, with the right-hand side carried as row n of the lower
+  // triangle: after step k, A[n][k] = y_k of L y = b (forward substitution comes for free).
+  if (tid < n) A[n][tid] = rhs[tid];
+  __syncthreads();
   for (int k = 0; k < n; ++k) {
-    if (tid == 0) A[k][k] = sqrt(A[k][k]);
+    const double dk = sqrt(A[k][k]);
+    if (tid > k && tid <= n) A[tid][k] /= dk;
+    if (tid == 0) rhs[k] = dk;                          // diagonal of L
     __syncthreads();
-    if (tid > k && tid < n) A[tid][k] /= A[k][k];
-    __syncthreads();
-    for (int v = tid; v < (n - k - 1) * (n - k - 1); v += 128) {
-      int i = k + 1 + v / (n - k - 1), j = k + 1 + v % (n - k - 1);
-      if (j <= i) A[i][j] -= A[i][k] * A[j][k];
+    const int m = n - k;                                // rows k+1..n (n is the rhs row)
+    for (int v = tid; v < m * m; v += blockDim.x) {
+      int i = k + 1 + v / m, j = k + 1 + v % m;
+      if (j <= i && j < n) A[i][j] -= A[i][k] * A[j][k];
     }
     __syncthreads();
   }
-  if (tid == 0) {
-    for (int i = 0; i < n; ++i) {
-      double t = rhs[i];
-      for (int j = 0; j < i; ++j) t -= A[i][j] * rhs[j];
-      rhs[i] = t / A[i][i];
-    }
-    for (int i = n - 1; i >= 0; --i) {
-      double t = rhs[i];
-      for (int j = i + 1; j < n; ++j) t -= A[j][i] * rhs[j];
-      rhs[i] = t / A[i][i];
-    }
+  // back substitution L^T x = y, column oriented: x_i = y_i / L_ii, then y_j -= L_ij x_i for j < i
+  for (int i = n - 1; i >= 0; --i) {
+    if (tid == 0) A[n][i] /= rhs[i];
+    __syncthreads();
+    if (tid < i) A[n][tid] -= A[i][tid] * A[n][i];
+    __syncthreads();
   }
+  if (tid < n) rhs[tid] = A[n][tid];
   __syncthreads();
   if (tid < n) {
     dxs[tid] = (float)rhs[tid];
