@@ -123,6 +123,17 @@ int qsp_get_iteration(qsp_decoder* dec, int32_t iteration, int32_t b, float* H, 
 int qsp_get_band_indices(qsp_decoder* dec, int32_t iteration, int32_t b, int32_t* ray,
                          int32_t* sample, int32_t cap);
 
+/* --- isosurface extraction: replaces reconstruct/utils.py:120-141 convert_sdf_voxels_to_mesh ------- */
+/* sdf (D,D,D) row-major (the grid decode of qsp_decode_sdf over create_voxel_grid(D));           */
+/* vertices (V,3) float32 = array index * spacing + origin, faces (F,3) int32.  Marching           */
+/* tetrahedra, not scikit-image's Lewiner tables (same zero level set, different triangulation).  */
+typedef struct qsp_mesh qsp_mesh;
+int qsp_mesh_extract(const float* sdf, int32_t D, float level, float spacing, const float* origin,
+                     uint32_t flags, void* stream, qsp_mesh** out);
+int qsp_mesh_sizes(const qsp_mesh* m, int32_t* n_vertices, int32_t* n_faces);
+int qsp_mesh_copy(const qsp_mesh* m, float* vertices, int32_t* faces);   /* host pointers */
+void qsp_mesh_free(qsp_mesh* m);
+
 /* --- bookkeeping --------------------------------------------------------------------------------- */
 const char* qsp_last_error(void);
 int64_t qsp_launch_count(void);                 /* kernels launched by this library so far */

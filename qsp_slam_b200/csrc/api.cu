@@ -12,6 +12,7 @@
 #include "decoder_ffma.cuh"
 #include "decoder_tc.cuh"
 #include "gn_kernels.cuh"
+#include "mesh_kernels.cuh"
 
 static thread_local std::string g_err;
 static std::atomic<long long> g_launches{0};
@@ -668,4 +669,80 @@ extern "C" int qsp_estimate_pose_batch(qsp_decoder* d, int32_t num_iterations, i
     CK(cudaStreamSynchronize(st));
   }
   return QSP_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// isosurface extraction (marching tetrahedra) - the step after the grid decode
+// ------------------------------------------------------------------------------------------------
+struct qsp_mesh {
+  float* verts = nullptr;   // device (nv,3)
+  int* faces = nullptr;     // device (nf,3)
+  int nv = 0, nf = 0;
+};
+
+extern "C" int qsp_mesh_extract(const float* sdf, int32_t D, float level, float spacing, const float* origin,
+                                uint32_t flags, void* stream, qsp_mesh** out) {
+  if (!sdf || !origin || !out || D < 2 || D > 1024) { g_err = "bad argument"; return QSP_ERR_INVALID; }
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t V = (size_t)D * D * D, Cn = (size_t)(D - 1) * (D - 1) * (D - 1);
+  float* dsdf = nullptr;
+  unsigned char* vmask = nullptr;
+  int *vcount = nullptr, *vbase = nullptr, *tcount = nullptr, *tbase = nullptr;
+  qsp_mesh* m = new qsp_mesh();
+  auto cleanup = [&]() {
+    if (flags & QSP_FLAG_HOST_PTRS) cudaFree(dsdf);
+    cudaFree(vmask); cudaFree(vcount); cudaFree(vbase); cudaFree(tcount); cudaFree(tbase);
+  };
+#define CKM(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { g_err = std::string(#call) + ": " + cudaGetErrorString(e_); cleanup(); cudaFree(m->verts); cudaFree(m->faces); delete m; return QSP_ERR_CUDA; } } while (0)
+  const float* src = sdf;
+  if (flags & QSP_FLAG_HOST_PTRS) {
+    CKM(cudaMalloc(&dsdf, V * 4));
+    CKM(cudaMemcpyAsync(dsdf, sdf, V * 4, cudaMemcpyHostToDevice, st));
+    src = dsdf;
+  }
+  CKM(cudaMalloc(&vmask, V));
+  CKM(cudaMalloc(&vcount, V * 4));
+  CKM(cudaMalloc(&vbase, (V + 1) * 4));
+  CKM(cudaMalloc(&tcount, Cn * 4));
+  CKM(cudaMalloc(&tbase, (Cn + 1) * 4));
+  const int tb = 256;
+  k_mt_vertex_flags<<<(unsigned)((V + tb - 1) / tb), tb, 0, st>>>(src, D, level, vmask, vcount); LAUNCHED();
+  k_exclusive_scan<<<1, 1024, 0, st>>>(vcount, vbase, (int)V, nullptr, 0, nullptr); LAUNCHED();
+  k_mt_cells<false><<<(unsigned)((Cn + tb - 1) / tb), tb, 0, st>>>(src, D, level, vmask, vbase, tcount, nullptr, nullptr); LAUNCHED();
+  k_exclusive_scan<<<1, 1024, 0, st>>>(tcount, tbase, (int)Cn, nullptr, 0, nullptr); LAUNCHED();
+  CKM(cudaMemcpyAsync(&m->nv, vbase + V, 4, cudaMemcpyDeviceToHost, st));
+  CKM(cudaMemcpyAsync(&m->nf, tbase + Cn, 4, cudaMemcpyDeviceToHost, st));
+  CKM(cudaStreamSynchronize(st));
+  CKM(cudaMalloc(&m->verts, (size_t)std::max(m->nv, 1) * 12));
+  CKM(cudaMalloc(&m->faces, (size_t)std::max(m->nf, 1) * 12));
+  k_mt_vertices<<<(unsigned)((V + tb - 1) / tb), tb, 0, st>>>(src, D, level, spacing, origin[0], origin[1], origin[2],
+                                                              vmask, vbase, m->verts); LAUNCHED();
+  k_mt_cells<true><<<(unsigned)((Cn + tb - 1) / tb), tb, 0, st>>>(src, D, level, vmask, vbase, nullptr, tbase, m->faces); LAUNCHED();
+  CKM(cudaGetLastError());
+  CKM(cudaStreamSynchronize(st));
+#undef CKM
+  cleanup();
+  *out = m;
+  return QSP_OK;
+}
+
+extern "C" int qsp_mesh_sizes(const qsp_mesh* m, int32_t* n_vertices, int32_t* n_faces) {
+  if (!m) return QSP_ERR_INVALID;
+  if (n_vertices) *n_vertices = m->nv;
+  if (n_faces) *n_faces = m->nf;
+  return QSP_OK;
+}
+
+extern "C" int qsp_mesh_copy(const qsp_mesh* m, float* vertices, int32_t* faces) {
+  if (!m) return QSP_ERR_INVALID;
+  if (vertices && m->nv) CK(cudaMemcpy(vertices, m->verts, (size_t)m->nv * 12, cudaMemcpyDeviceToHost));
+  if (faces && m->nf) CK(cudaMemcpy(faces, m->faces, (size_t)m->nf * 12, cudaMemcpyDeviceToHost));
+  return QSP_OK;
+}
+
+extern "C" void qsp_mesh_free(qsp_mesh* m) {
+  if (!m) return;
+  cudaFree(m->verts);
+  cudaFree(m->faces);
+  delete m;
 }
