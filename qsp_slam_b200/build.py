@@ -7,7 +7,7 @@ import subprocess
 HERE = os.path.dirname(os.path.abspath(__file__))
 LIB = os.path.join(HERE, "libqsp_recon.so")
 SOURCES = [os.path.join(HERE, "csrc", "api.cu")]
-HEADERS = [os.path.join(HERE, "csrc", f) for f in ("common.cuh", "decoder_ffma.cuh", "gn_kernels.cuh")] + \
+HEADERS = [os.path.join(HERE, "csrc", f) for f in ("common.cuh", "decoder_ffma.cuh", "decoder_tc.cuh", "decoder_t3.cuh", "tc_common.cuh", "gn_kernels.cuh", "mesh_kernels.cuh")] + \
           [os.path.join(os.path.dirname(HERE), "include", "qsp_recon.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]
@@ -24,7 +24,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not needs_build():
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + SOURCES + ["-o", LIB]
+    extra = os.environ.get("QSP_NVCC_EXTRA", "").split()    # experiments only, e.g. -DTC_NG=4
+    cmd = [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + SOURCES + ["-o", LIB]
     subprocess.run(cmd, check=True, cwd=os.path.join(HERE, "csrc"))
     return LIB
 

@@ -11,6 +11,7 @@
 #include "../../include/qsp_recon.h"
 #include "decoder_ffma.cuh"
 #include "decoder_tc.cuh"
+#include "decoder_t3.cuh"
 #include "gn_kernels.cuh"
 #include "mesh_kernels.cuh"
 
@@ -59,6 +60,11 @@ struct qsp_decoder {
   std::vector<int> h_rays_off;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   float last_ms = 0.f;
+  bool t3 = false;
+  bool pair = true;                                // CTA pairs (cta_group::2) for k_decoder_tc
+  int pair_grid = 148;
+  int cluster = 2;                                 // CTAs per cluster sharing a multicast weight stream
+  int t3_grid = 148;
 };
 
 template <typename T>
@@ -155,7 +161,32 @@ static int build_tc_images(qsp_decoder* d, const std::vector<std::vector<float>>
         }
       }
   }
-  void *pf = nullptr, *ps = nullptr;
+  // k_decoder_t3 stream: 128-row A-operand images in the order (step, half, k-block, M-tile, hi then lo)
+  std::vector<__half> t3;
+  for (int s = 0; s < 16; ++s) {
+    const bool fwd = s < 8;
+    const int l = fwd ? s : 15 - s, nm = s == 15 ? 1 : 4, nkb = s == 0 ? 2 : 8;
+    for (int h = 0; 2 * h < nm; ++h)
+      for (int kb = 0; kb < nkb; ++kb)
+        for (int m = 2 * h; m < std::min(nm, 2 * h + 2); ++m) {
+          const size_t base = t3.size();
+          t3.resize(base + 2 * (T3_TILE_BYTES / 2));
+          for (int r = 0; r < 128; ++r)
+            for (int k = 0; k < 64; ++k) {
+              const size_t in_tile = ((r / 8) * 1024 + (r % 8) * 128 + (((k / 8) ^ (r % 8)) * 16) + (k % 8) * 2) / 2;
+              const float v = TC_SW * (fwd ? w_at(l, m * 128 + r, kb * 64 + k)     // A[m = out][k = in]
+                                           : w_at(l, kb * 64 + k, m * 128 + r));   // A[m = in][k = out]
+              const __half hh = __float2half_rn(v);
+              t3[base + in_tile] = hh;
+              t3[base + T3_TILE_BYTES / 2 + in_tile] = __float2half_rn(v - __half2float(hh));
+            }
+        }
+  }
+  void *pf = nullptr, *ps = nullptr, *pt = nullptr;
+  CK(cudaMalloc(&pt, t3.size() * 2));
+  d->weight_allocs.push_back(pt);
+  CK(cudaMemcpy(pt, t3.data(), t3.size() * 2, cudaMemcpyHostToDevice));
+  d->tc.img_t3 = reinterpret_cast<const uint8_t*>(pt);
   CK(cudaMalloc(&pf, fast.size() * 2));
   d->weight_allocs.push_back(pf);
   CK(cudaMalloc(&ps, split.size() * 2));
@@ -220,9 +251,52 @@ extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_
   if ((r = build_tc_images(d, Wall)) || (r = upload(d, bias_all, &d->tc.bias))) { qsp_decoder_destroy(d); return r; }
   d->tc.w8 = d->dw.w8;
   d->tc.b8 = d->dw.b8;
-  CK(cudaFuncSetAttribute(k_decoder_tc<TC_FAST, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-  CK(cudaFuncSetAttribute(k_decoder_tc<TC_SPLIT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-  CK(cudaFuncSetAttribute(k_decoder_tc<TC_SPLIT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+  CK(cudaFuncSetAttribute(k_decoder_tc<TC_FAST, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+  CK(cudaFuncSetAttribute(k_decoder_tc<TC_SPLIT, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+  CK(cudaFuncSetAttribute(k_decoder_tc<TC_SPLIT, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+  CK(cudaFuncSetAttribute(k_decoder_tc<TC_FAST, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+  CK(cudaFuncSetAttribute(k_decoder_tc<TC_SPLIT, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+  CK(cudaFuncSetAttribute(k_decoder_tc<TC_SPLIT, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+  if (const char* e2 = getenv("QSP_TC_PAIR")) d->pair = atoi(e2) != 0;
+  d->t3 = getenv("QSP_TC_T3") != nullptr;             // A/B switch: the transposed three-product kernel k_decoder_t3
+  {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(d->num_sms / 2 * 2));
+    cfg.blockDim = dim3(TC_THREADS);
+    cfg.dynamicSmemBytes = TC_SMEM_BYTES;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    int ncl = 0;
+    cudaError_t e = cudaOccupancyMaxActiveClusters(&ncl, k_decoder_tc<TC_SPLIT, true, 2>, &cfg);
+    d->pair_grid = (e == cudaSuccess && ncl > 0) ? ncl * 2 : d->num_sms / 2 * 2;
+  }
+  CK(cudaFuncSetAttribute(k_decoder_t3<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, T3_SMEM_BYTES));
+  CK(cudaFuncSetAttribute(k_decoder_t3<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, T3_SMEM_BYTES));
+  CK(cudaFuncSetAttribute(k_decoder_t3<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, T3_SMEM_BYTES));
+  CK(cudaFuncSetAttribute(k_decoder_t3<true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, T3_SMEM_BYTES));
+  CK(cudaFuncSetAttribute(k_decoder_t3<false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, T3_SMEM_BYTES));
+  CK(cudaFuncSetAttribute(k_decoder_t3<true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, T3_SMEM_BYTES));
+  if (const char* cl_env = getenv("QSP_TC_CLUSTER")) d->cluster = atoi(cl_env);
+  if (d->cluster != 1 && d->cluster != 2 && d->cluster != 4) d->cluster = 2;
+  {
+    // persistent grid = the number of CTAs that can be co-resident as clusters of this size
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(d->num_sms / d->cluster * d->cluster));
+    cfg.blockDim = dim3(T3_THREADS);
+    cfg.dynamicSmemBytes = T3_SMEM_BYTES;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = d->cluster; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at; cfg.numAttrs = 1;
+    int ncl = 0;
+    cudaError_t e = d->cluster == 4 ? cudaOccupancyMaxActiveClusters(&ncl, k_decoder_t3<true, 4>, &cfg)
+                  : d->cluster == 2 ? cudaOccupancyMaxActiveClusters(&ncl, k_decoder_t3<true, 2>, &cfg)
+                                    : cudaOccupancyMaxActiveClusters(&ncl, k_decoder_t3<true, 1>, &cfg);
+    d->t3_grid = (e == cudaSuccess && ncl > 0) ? ncl * d->cluster : d->num_sms / d->cluster * d->cluster;
+    if (getenv("QSP_TC_VERBOSE")) fprintf(stderr, "qsp: t3 cluster %d, %d co-resident clusters, grid %d\n", d->cluster, ncl, d->t3_grid);
+  }
   CK(cudaFuncSetAttribute(k_decoder_ffma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FF_SMEM_BYTES));
   CK(cudaFuncSetAttribute(k_decoder_ffma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FF_SMEM_BYTES));
   if (const char* dbg_env = getenv("QSP_TC_DEBUG")) {
@@ -269,6 +343,50 @@ extern "C" int qsp_kernel_ms(qsp_decoder* d, float* ms) {
 // ------------------------------------------------------------------------------------------------
 enum DecMode { DEC_FP32 = 0, DEC_SPLIT = 1, DEC_FAST = 2 };
 
+// launches a decoder kernel as thread-block clusters of CL CTAs (CL = 1: plain launch)
+template <class K>
+static int launch_clustered(K kernel, int grid, int cl, size_t smem, cudaStream_t st, const TcDecoderDev& tc, const float* pts,
+                            const int* code_idx, const float* codes, int code_stride, int n_codes_y, long n, const int* n_dev,
+                            float* sdf, float* jacp) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)((grid + cl - 1) / cl * cl));
+  cfg.blockDim = dim3(TC_THREADS);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = cl; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  CK(cudaLaunchKernelEx(&cfg, kernel, tc, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp));
+  return QSP_OK;
+}
+
+// k_decoder_t3 as thread-block clusters of d->cluster CTAs that share one multicast weight stream
+template <bool JAC, int CL>
+static int launch_t3_cl(int grid, const TcDecoderDev& tc, const float* pts, const int* code_idx, const float* codes,
+                        int code_stride, int n_codes_y, long n, const int* n_dev, float* sdf, float* jacp, cudaStream_t st) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)((grid + CL - 1) / CL * CL));
+  cfg.blockDim = dim3(T3_THREADS);
+  cfg.dynamicSmemBytes = T3_SMEM_BYTES;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = CL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  CK(cudaLaunchKernelEx(&cfg, k_decoder_t3<JAC, CL>, tc, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp));
+  return QSP_OK;
+}
+static int launch_t3(qsp_decoder* d, bool jac, int grid, const float* pts, const int* code_idx, const float* codes,
+                     int code_stride, int n_codes_y, long n, const int* n_dev, float* sdf, float* jacp, cudaStream_t st) {
+  grid = std::min(grid, d->t3_grid);
+#define T3_CASE(J, C) return launch_t3_cl<J, C>(grid, d->tc, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp, st)
+  if (d->cluster == 4) { if (jac) T3_CASE(true, 4); else T3_CASE(false, 4); }
+  if (d->cluster == 2) { if (jac) T3_CASE(true, 2); else T3_CASE(false, 2); }
+  if (jac) T3_CASE(true, 1); else T3_CASE(false, 1);
+#undef T3_CASE
+}
+
 static int launch_decoder(qsp_decoder* d, int mode, bool jac, const float* pts, const int* code_idx, const float* codes,
                           int code_stride, long n, const int* n_dev, int n_codes_y, float* sdf, float* jacp,
                           cudaStream_t st) {
@@ -277,12 +395,25 @@ static int launch_decoder(qsp_decoder* d, int mode, bool jac, const float* pts, 
   if (tiles <= 0) return QSP_OK;
   dim3 grid((unsigned)std::min<long>(tiles, d->num_sms));   // persistent: one CTA per SM
   if (mode != DEC_FP32) {
+#define TC_LAUNCH(M, J)                                                                                              \
+  do {                                                                                                               \
+    int r_ = d->pair ? launch_clustered(k_decoder_tc<M, J, 2>, std::min<int>(grid.x, d->pair_grid), 2, TC_SMEM_BYTES, st, d->tc, pts, \
+                                        code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp)               \
+                     : launch_clustered(k_decoder_tc<M, J, 1>, grid.x, 1, TC_SMEM_BYTES, st, d->tc, pts, code_idx, codes, \
+                                        code_stride, n_codes_y, n, n_dev, sdf, jacp);                               \
+    if (r_) return r_;                                                                                               \
+  } while (0)
     if (mode == DEC_FAST && !jac)
-      k_decoder_tc<TC_FAST, false><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(d->tc, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
+      TC_LAUNCH(TC_FAST, false);
+    else if (d->t3) {
+      int r = launch_t3(d, jac, grid.x, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp, st);
+      if (r) return r;
+    }
     else if (!jac)
-      k_decoder_tc<TC_SPLIT, false><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(d->tc, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
+      TC_LAUNCH(TC_SPLIT, false);
     else
-      k_decoder_tc<TC_SPLIT, true><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(d->tc, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
+      TC_LAUNCH(TC_SPLIT, true);
+#undef TC_LAUNCH
     LAUNCHED();
     CK(cudaGetLastError());
     return QSP_OK;

@@ -33,7 +33,7 @@
 #define TC_STAGES 3
 #define TC_TILE_BYTES 32768                       // one [256][64] fp16 weight image
 #define TC_ABLK_BYTES 16384                       // one [128][64] fp16 activation K-block
-#define TC_SMEM_BYTES (8 * TC_ABLK_BYTES + TC_STAGES * TC_TILE_BYTES + 256 + 2048)
+#define TC_SMEM_BYTES (8 * TC_ABLK_BYTES + TC_STAGES * TC_TILE_BYTES + 512 + 2048)
 #define TC_SA 16.0f                               // activation scale (split mode): keeps lo parts normal in fp16
 #define TC_SW 16.0f                               // weight scale (split mode)
 #define TC_SG 256.0f                              // gradient scale of the reverse sweep (split mode)
@@ -45,6 +45,7 @@ __device__ int g_tc_dbg = 0;
 struct TcDecoderDev {
   const uint8_t* img_fast;                        // forward weight images, fp16(W), consumption order
   const uint8_t* img_split;                       // forward then reverse images, (hi, lo) interleaved per tile
+  const uint8_t* img_t3;                          // k_decoder_t3: [128 m][64 k] images, (step, half, k-block, M-tile, hi/lo)
   const float* bias;                              // [8][512] fp32, zero padded
   const float* w8;                                // [512] fp32
   float b8;
@@ -76,7 +77,15 @@ __device__ __forceinline__ int tc_step_halves(int s) { return s == 15 ? 1 : 2; }
 //   acc_free[h]        the epilogue has read accumulator half h of step it (256 arrivals)
 // This lets the epilogue of half 0 run under the MMAs of half 1, and the epilogue of half 1 under the
 // MMAs of the next layer's half 0: the tensor pipe only waits for K-blocks that are not yet rewritten.
-template <int MODE, bool JAC>
+//
+// CG = 2 runs the kernel as CTA pairs (thread-block clusters of 2) with tcgen05.mma.cta_group::2: the pair
+// computes M = 256 (each CTA's own 128 rows of A', its own TMEM) against ONE weight tile whose two N-halves
+// live in the two CTAs' shared memories -- each CTA streams only half of the weights, which halves the
+// shared-memory write traffic of the ring and the B-operand read traffic per CTA (shared memory bandwidth,
+// 128 B/clk/SM, is what bounds the single-CTA version: 12 KB of operand reads + 8 KB of ring writes per
+// 128-cycle MMA).  The leader CTA (cluster rank 0) issues every MMA; its barriers collect the arrivals of
+// both CTAs (a_ready, acc_free, full), and its commits are multicast to both (empty, a_free, acc_full).
+template <int MODE, bool JAC, int CG>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restrict__ code_idx,
              const float* __restrict__ codes, int code_stride, int n_codes, long n_host,
@@ -89,34 +98,47 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = smem_raw;                              // checked below: must be 1024-byte aligned
   uint8_t* sA = smem;                                    // 8 x 16 KB
-  uint8_t* sB = smem + 8 * TC_ABLK_BYTES;                // TC_STAGES x 32 KB
+  constexpr int NST = TC_STAGES * CG;                    // ring stages
+  constexpr int STAGE_BYTES = TC_TILE_BYTES / CG;        // this CTA's share of a weight tile: [256 / CG n][64 k]
+  uint8_t* sB = smem + 8 * TC_ABLK_BYTES;                // NST x STAGE_BYTES = 96 KB
   uint64_t* bars = reinterpret_cast<uint64_t*>(sB + TC_STAGES * TC_TILE_BYTES);
-  uint64_t* full = bars;                                 // [3]
-  uint64_t* empty = bars + 3;                            // [3]
-  uint64_t* acc_full = bars + 6;                         // [2]
-  uint64_t* acc_free = bars + 8;                         // [2]
-  uint64_t* a_ready = bars + 10;                         // [8]
-  uint64_t* a_free = bars + 18;                          // [8]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 26);
-  float* sbias = reinterpret_cast<float*>(bars + 32);    // [512] bias of the current layer
+  uint64_t* full = bars;                                 // [NST <= 6]
+  uint64_t* empty = bars + 6;                            // [NST]
+  uint64_t* acc_full = bars + 12;                        // [2]
+  uint64_t* acc_free = bars + 14;                        // [2]
+  uint64_t* a_ready = bars + 16;                         // [8]
+  uint64_t* a_free = bars + 24;                          // [8]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 32);
+  float* sbias = reinterpret_cast<float*>(bars + 64);    // [512] bias of the current layer
   float* part = sbias;                                   // [2][128] lin8 partial sums (aliases sbias)
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const long n = n_dev ? (long)(*n_dev) : n_host;
   const long ntiles = (n + ROWS - 1) / ROWS;
   const long total_tiles = ntiles * n_codes;
+  // both CTAs of a pair walk the same number of tiles; a surplus tile has no valid rows
+  const long iters = (total_tiles + gridDim.x - 1) / gridDim.x;
+  const uint32_t crank = CG == 2 ? cluster_ctarank() : 0;
+  const bool leader = crank == 0;
 
   if (tid == 0) {
     if (smem_u32(smem) & 1023) asm volatile("trap;");
-    for (int i = 0; i < TC_STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_free[i], TC_EPI); }
-    for (int i = 0; i < 8; ++i) { mbar_init(&a_ready[i], 128); mbar_init(&a_free[i], 1); }
+    // arrivals are one elected lane per warp; the leader's barriers also count the peer CTA's warps
+    for (int i = 0; i < NST; ++i) { mbar_init(&full[i], (CG == 2 && leader) ? 2 : 1); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_free[i], CG * (TC_EPI / 32)); }
+    for (int i = 0; i < 8; ++i) { mbar_init(&a_ready[i], CG * 4); mbar_init(&a_free[i], 1); }
     fence_mbar_init();
   }
-  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  if (warp == 1) { if (CG == 2) tmem_alloc2(tmem_slot, 512); else tmem_alloc(tmem_slot, 512); }
   tc_fence_before();
   __syncthreads();
+  if (CG == 2) cluster_sync_all();                       // the peer's barriers exist before anything signals them
   tc_fence_after();
+  // one arrival per warp (after every lane's writes / TMEM reads are fenced), on the leader's barrier
+  auto warp_arrive = [&](uint64_t* bar) {
+    __syncwarp();
+    if (lane == 0) { if (CG == 2) mbar_arrive_cta(bar, 0); else mbar_arrive(bar); }
+  };
   const uint32_t tmem = *tmem_slot;
   const int dbg = g_tc_dbg;
 
@@ -124,18 +146,18 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
     // ================= weight producer =================
     if (lane == 0) {
       int stage = 0; uint32_t ph = 0;
-      const uint8_t* base = MODE == TC_SPLIT ? dw.img_split : dw.img_fast;
-      for (long gt = blockIdx.x; gt < total_tiles; gt += gridDim.x) {
+      const uint8_t* base = (MODE == TC_SPLIT ? dw.img_split : dw.img_fast) + crank * STAGE_BYTES;
+      for (long i = 0; i < iters; ++i) {
         const uint8_t* src = base;
         for (int s = 0; s < NSTEPS; ++s) {
           const int nt = tc_step_halves(s) * tc_step_kblocks(s) * TPB;
           for (int t = 0; t < nt; ++t) {
             mbar_wait(&empty[stage], ph ^ 1);
-            if (dbg & 1) { mbar_arrive(&full[stage]); src += TC_TILE_BYTES; if (++stage == TC_STAGES) { stage = 0; ph ^= 1; } continue; }
-            mbar_expect_tx(&full[stage], TC_TILE_BYTES);
-            bulk_g2s(sB + stage * TC_TILE_BYTES, src, TC_TILE_BYTES, &full[stage]);
+            if (dbg & 1) { mbar_arrive(&full[stage]); src += TC_TILE_BYTES; if (++stage == NST) { stage = 0; ph ^= 1; } continue; }
+            mbar_expect_tx(&full[stage], STAGE_BYTES);
+            bulk_g2s(sB + stage * STAGE_BYTES, src, STAGE_BYTES, &full[stage]);
             src += TC_TILE_BYTES;
-            if (++stage == TC_STAGES) { stage = 0; ph ^= 1; }
+            if (++stage == NST) { stage = 0; ph ^= 1; }
           }
         }
       }
@@ -143,38 +165,52 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
   } else if (warp == 1) {
     // ================= MMA issuer =================
     int stage = 0; uint32_t ph = 0, it = 0;
-    const uint32_t idesc = make_idesc_f16(128, 256);
-    for (long gt = blockIdx.x; gt < total_tiles; gt += gridDim.x) {
+    const uint32_t idesc = make_idesc_f16(128 * CG, 256);
+    if (CG == 2 && !leader) {
+      // peer CTA: forward "my half of the weight tile has landed" to the leader's full barrier
+      for (long i = 0; i < iters; ++i)
+        for (int s = 0; s < NSTEPS; ++s) {
+          const int nt = tc_step_halves(s) * tc_step_kblocks(s) * TPB;
+          for (int t = 0; t < nt; ++t) {
+            mbar_wait(&full[stage], ph);
+            if (lane == 0) mbar_arrive_cta(&full[stage], 0);
+            __syncwarp();
+            if (++stage == NST) { stage = 0; ph ^= 1; }
+          }
+        }
+    } else
+    for (long i = 0; i < iters; ++i) {
       for (int s = 0; s < NSTEPS; ++s, ++it) {
         const uint32_t par = it & 1;
         const int nh = tc_step_halves(s), nkb = tc_step_kblocks(s);
         for (int h = 0; h < 2; ++h) {
-          mbar_wait(&acc_free[h], par ^ 1);              // previous step's epilogue has drained this half
+          mbar_wait_cl(&acc_free[h], par ^ 1);           // previous step's epilogue has drained this half
           tc_fence_after();
           if (h < nh) {
             for (int kb = 0; kb < nkb; ++kb) {
-              if (h == 0) { mbar_wait(&a_ready[kb], par); tc_fence_after(); }
+              if (h == 0) { mbar_wait_cl(&a_ready[kb], par); tc_fence_after(); }
               for (int t = 0; t < TPB; ++t) {
-                mbar_wait(&full[stage], ph);
+                mbar_wait_cl(&full[stage], ph);
                 tc_fence_after();
                 if (elect_one()) {
 #pragma unroll
                   for (int k = 0; k < 4; ++k) {
                     uint64_t da = make_sdesc_sw128(sA + kb * TC_ABLK_BYTES + k * 32);
-                    uint64_t db = make_sdesc_sw128(sB + stage * TC_TILE_BYTES + k * 32);
-                    umma_f16(tmem + h * 256, da, db, idesc, (kb | t | k) != 0);
+                    uint64_t db = make_sdesc_sw128(sB + stage * STAGE_BYTES + k * 32);
+                    if (CG == 2) umma_f16_2cta(tmem + h * 256, da, db, idesc, (kb | t | k) != 0);
+                    else umma_f16(tmem + h * 256, da, db, idesc, (kb | t | k) != 0);
                   }
-                  umma_commit(&empty[stage]);
-                  if (h == nh - 1 && t == TPB - 1) umma_commit(&a_free[kb]);
+                  if (CG == 2) umma_commit2_mc(&empty[stage], 3); else umma_commit(&empty[stage]);
+                  if (h == nh - 1 && t == TPB - 1) { if (CG == 2) umma_commit2_mc(&a_free[kb], 3); else umma_commit(&a_free[kb]); }
                 }
                 __syncwarp();
-                if (++stage == TC_STAGES) { stage = 0; ph ^= 1; }
+                if (++stage == NST) { stage = 0; ph ^= 1; }
               }
             }
           }
           if (elect_one()) {
-            umma_commit(&acc_full[h]);
-            if (h == 1) for (int kb = nkb; kb < 8; ++kb) umma_commit(&a_free[kb]);
+            if (CG == 2) umma_commit2_mc(&acc_full[h], 3); else umma_commit(&acc_full[h]);
+            if (h == 1) for (int kb = nkb; kb < 8; ++kb) { if (CG == 2) umma_commit2_mc(&a_free[kb], 3); else umma_commit(&a_free[kb]); }
           }
           __syncwarp();
         }
@@ -203,10 +239,13 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
         uint32_t hi[8], lo[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) split2(f[2 * j] * sc, f[2 * j + 1] * sc, hi[j], lo[j]);
-        *reinterpret_cast<uint4*>(blk + sw128_offset(row_hi, c16)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
-        *reinterpret_cast<uint4*>(blk + sw128_offset(row_hi, c16 + 1)) = make_uint4(hi[4], hi[5], hi[6], hi[7]);
-        *reinterpret_cast<uint4*>(blk + sw128_offset(row_lo, c16)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
-        *reinterpret_cast<uint4*>(blk + sw128_offset(row_lo, c16 + 1)) = make_uint4(lo[4], lo[5], lo[6], lo[7]);
+        // lanes 2i / 2i+1 write the same rows, chunks {c, c+1} / {c+2, c+3}: the odd lane stores its chunks in
+        // the opposite order so that a quarter-warp always hits 8 distinct 16-byte bank groups
+        const int o0 = odd ? 1 : 0, o1 = o0 ^ 1;
+        *reinterpret_cast<uint4*>(blk + sw128_offset(row_hi, c16 + o0)) = odd ? make_uint4(hi[4], hi[5], hi[6], hi[7]) : make_uint4(hi[0], hi[1], hi[2], hi[3]);
+        *reinterpret_cast<uint4*>(blk + sw128_offset(row_hi, c16 + o1)) = odd ? make_uint4(hi[0], hi[1], hi[2], hi[3]) : make_uint4(hi[4], hi[5], hi[6], hi[7]);
+        *reinterpret_cast<uint4*>(blk + sw128_offset(row_lo, c16 + o0)) = odd ? make_uint4(lo[4], lo[5], lo[6], lo[7]) : make_uint4(lo[0], lo[1], lo[2], lo[3]);
+        *reinterpret_cast<uint4*>(blk + sw128_offset(row_lo, c16 + o1)) = odd ? make_uint4(lo[0], lo[1], lo[2], lo[3]) : make_uint4(lo[4], lo[5], lo[6], lo[7]);
       } else {
 #pragma unroll
         for (int u = 0; u < 4; ++u)
@@ -216,8 +255,10 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
       }
     };
 
-    for (long gt = blockIdx.x; gt < total_tiles; gt += gridDim.x) {
-      const long cy = gt / ntiles, tile = gt - cy * ntiles;
+    for (long i = 0; i < iters; ++i) {
+      const long gt = i * gridDim.x + blockIdx.x;
+      const bool live = gt < total_tiles;                // surplus tile: every row is invalid
+      const long cy = live ? gt / ntiles : 0, tile = live ? gt - cy * ntiles : ntiles;
       const float* pass_code = codes + (size_t)cy * code_stride;
       float* sdf_o = sdf_out ? sdf_out + (size_t)cy * n : nullptr;
       const long grow = tile * ROWS + pl;                // global row of this thread's point
@@ -261,7 +302,7 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
           fence_proxy_async();
         }
 #pragma unroll
-        for (int u = 0; u < 2 * KPG; ++u) mbar_arrive(&a_ready[(u / KPG) * 4 + KPG * g + (u % KPG)]);
+        for (int u = 0; u < 2 * KPG; ++u) warp_arrive(&a_ready[(u / KPG) * 4 + KPG * g + (u % KPG)]);
       }
       float sdf_v = 0.f;
 
@@ -296,7 +337,7 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
               if (dbg & 2) {
                 if (rewrite) {
                   if ((cc & 1) == 0) mbar_wait(&a_free[kb], par);
-                  if (cc & 1) { fence_proxy_async(); mbar_arrive(&a_ready[kb]); }
+                  if (cc & 1) { fence_proxy_async(); warp_arrive(&a_ready[kb]); }
                 }
                 continue;
               }
@@ -307,7 +348,7 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
                 if (v[0] == 0x7fc12345u && v[31] == 0x7fc54321u) psum += 1.f;
                 if (rewrite) {
                   if ((cc & 1) == 0) mbar_wait(&a_free[kb], par);
-                  if (cc & 1) { fence_proxy_async(); mbar_arrive(&a_ready[kb]); }
+                  if (cc & 1) { fence_proxy_async(); warp_arrive(&a_ready[kb]); }
                 }
                 continue;
               }
@@ -391,12 +432,12 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
                 if ((cc & 1) == 0) mbar_wait(&a_free[kb], par);   // this step's MMAs are done with K-block kb
                 if (!(dbg & 8)) store_cols(f, colb, (MODE == TC_SPLIT && fwd) ? TC_SA : 1.f);
                 else if (f[0] == 123.456f) psum += f[CW - 1];
-                if (cc & 1) { fence_proxy_async(); mbar_arrive(&a_ready[kb]); }
+                if (cc & 1) { fence_proxy_async(); warp_arrive(&a_ready[kb]); }
               }
             }
           }
           tc_fence_before();
-          mbar_arrive(&acc_free[h]);
+          warp_arrive(&acc_free[h]);
         }
         if (JAC && fwd) {
 #pragma unroll
@@ -437,7 +478,7 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
               }
               if ((cc & 1) == 0) mbar_wait(&a_free[kb], par);
               store_cols(gsd, colb, 1.f);
-              if (cc & 1) { fence_proxy_async(); mbar_arrive(&a_ready[kb]); }
+              if (cc & 1) { fence_proxy_async(); warp_arrive(&a_ready[kb]); }
             }
           }
         }
@@ -446,5 +487,6 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem, 512);
+  if (CG == 2) cluster_sync_all();                       // the pair retires together (remote arrivals, peer smem reads)
+  if (warp == 1) { if (CG == 2) tmem_dealloc2(tmem, 512); else tmem_dealloc(tmem, 512); }
 }
