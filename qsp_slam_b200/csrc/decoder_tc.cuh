@@ -126,7 +126,7 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
     // arrivals are one elected lane per warp; the leader's barriers also count the peer CTA's warps
     for (int i = 0; i < NST; ++i) { mbar_init(&full[i], (CG == 2 && leader) ? 2 : 1); mbar_init(&empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_free[i], CG * (TC_EPI / 32)); }
-    for (int i = 0; i < 8; ++i) { mbar_init(&a_ready[i], CG * 4); mbar_init(&a_free[i], 1); }
+    for (int i = 0; i < 8; ++i) { mbar_init(&a_ready[i], CG * (TC_EPI / 32)); mbar_init(&a_free[i], 1); }
     fence_mbar_init();
   }
   if (warp == 1) { if (CG == 2) tmem_alloc2(tmem_slot, 512); else tmem_alloc(tmem_slot, 512); }
@@ -265,11 +265,11 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
       const bool valid = grow < n;
       const float* my_code = (code_idx && valid) ? codes + (size_t)code_idx[grow] * code_stride : pass_code;
       // ---- stage the input rows [code, xyz, 0...] into K-blocks 0,1 (loss_utils.py:71-72) ----
-      // group g owns K-blocks {2g, 2g+1, 4+2g, 4+2g+1}; group 0 writes K-blocks 0 and 1 here.
+      // chunk cc of group g covers columns (cc*TC_NG + g)*32 of a half, so all warps finish K-block 4h+cc together; group 0 stages K-blocks 0 and 1 here.
       {
         const uint32_t prev = (it & 1) ^ 1;              // the previous step's MMAs released the K-blocks
 #pragma unroll
-        for (int u = 0; u < 2 * KPG; ++u) mbar_wait(&a_free[(u / KPG) * 4 + KPG * g + (u % KPG)], prev);
+        for (int u = 0; u < 8; ++u) mbar_wait(&a_free[u], prev);
         if (g * KPG < 2) {                               // the groups that own K-blocks 0 and 1
           const int rr = e & 127;                        // A' row 0..127
           const int ip = MODE == TC_SPLIT ? (rr >> 1) : rr;
@@ -302,7 +302,7 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
           fence_proxy_async();
         }
 #pragma unroll
-        for (int u = 0; u < 2 * KPG; ++u) warp_arrive(&a_ready[(u / KPG) * 4 + KPG * g + (u % KPG)]);
+        for (int u = 0; u < 8; ++u) warp_arrive(&a_ready[u]);
       }
       float sdf_v = 0.f;
 
@@ -327,28 +327,28 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
           if (h < nh) {
             // software pipeline: the TMEM load of chunk cc+1 is in flight while chunk cc is processed
             uint32_t vbuf[2][32];
-            const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + h * 256 + g * (NCH * 32);
+            const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + h * 256 + g * 32;
             if (!(dbg & 2)) tmem_ld32(tbase, vbuf[0]);
 #pragma unroll
             for (int cc = 0; cc < NCH; ++cc) {
-              const int col0 = h * 256 + g * (NCH * 32) + cc * 32;
+              const int col0 = h * 256 + (cc * TC_NG + g) * 32;
               const int kb = col0 >> 6;
               const int bit0 = (h * NCH + cc) * CW;
               if (dbg & 2) {
                 if (rewrite) {
-                  if ((cc & 1) == 0) mbar_wait(&a_free[kb], par);
-                  if (cc & 1) { fence_proxy_async(); warp_arrive(&a_ready[kb]); }
+                  mbar_wait(&a_free[kb], par);
+                  { fence_proxy_async(); warp_arrive(&a_ready[kb]); }
                 }
                 continue;
               }
               tmem_ld_wait();
-              if (cc + 1 < NCH) tmem_ld32(tbase + (cc + 1) * 32, vbuf[(cc + 1) & 1]);
+              if (cc + 1 < NCH) tmem_ld32(tbase + (cc + 1) * (TC_NG * 32), vbuf[(cc + 1) & 1]);
               uint32_t (&v)[32] = vbuf[cc & 1];
               if (dbg & 4) {                               // timing experiment: TMEM reads only
                 if (v[0] == 0x7fc12345u && v[31] == 0x7fc54321u) psum += 1.f;
                 if (rewrite) {
-                  if ((cc & 1) == 0) mbar_wait(&a_free[kb], par);
-                  if (cc & 1) { fence_proxy_async(); warp_arrive(&a_ready[kb]); }
+                  mbar_wait(&a_free[kb], par);
+                  { fence_proxy_async(); warp_arrive(&a_ready[kb]); }
                 }
                 continue;
               }
@@ -429,10 +429,10 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
                 }
               }
               if (rewrite) {
-                if ((cc & 1) == 0) mbar_wait(&a_free[kb], par);   // this step's MMAs are done with K-block kb
+                mbar_wait(&a_free[kb], par);   // this step's MMAs are done with K-block kb
                 if (!(dbg & 8)) store_cols(f, colb, (MODE == TC_SPLIT && fwd) ? TC_SA : 1.f);
                 else if (f[0] == 123.456f) psum += f[CW - 1];
-                if (cc & 1) { fence_proxy_async(); warp_arrive(&a_ready[kb]); }
+                { fence_proxy_async(); warp_arrive(&a_ready[kb]); }
               }
             }
           }
@@ -462,7 +462,7 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
 #pragma unroll 1
             for (int c8 = 0; c8 < 2 * NCH; ++c8) {
               const int h = c8 / NCH, cc = c8 % NCH;
-              const int col0 = h * 256 + g * (NCH * 32) + cc * 32, kb = col0 >> 6;
+              const int col0 = h * 256 + (cc * TC_NG + g) * 32, kb = col0 >> 6;
               const int colb = col0 + (odd ? 16 : 0), bit0 = (h * NCH + cc) * 16;
               float gsd[16];
 #pragma unroll
@@ -476,9 +476,9 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
                   gsd[j] = keep ? d * ww[u] : 0.f;
                 }
               }
-              if ((cc & 1) == 0) mbar_wait(&a_free[kb], par);
+              mbar_wait(&a_free[kb], par);
               store_cols(gsd, colb, 1.f);
-              if (cc & 1) { fence_proxy_async(); warp_arrive(&a_ready[kb]); }
+              { fence_proxy_async(); warp_arrive(&a_ready[kb]); }
             }
           }
         }

@@ -376,7 +376,7 @@ k_accumulate(const ObjState* __restrict__ st, const int* __restrict__ pts_off,
              const float* __restrict__ g_jac, const float* __restrict__ row_fac,
              const float* __restrict__ row_res, float b_sdf, float b_render, int pose_only,
              const float* __restrict__ row_active, float* __restrict__ partials) {
-  __shared__ float J[GN_SLOT][73];
+  __shared__ __align__(16) float J[GN_SLOT][72];
   const int chunk = blockIdx.x, nchunk = gridDim.x, o = blockIdx.y, term = blockIdx.z;
   const int tid = threadIdx.x;
   float* out = partials + (((size_t)o * 2 + term) * nchunk + chunk) * QSP_PART_STRIDE;
@@ -385,18 +385,20 @@ k_accumulate(const ObjState* __restrict__ st, const int* __restrict__ pts_off,
   else { start = M_total + band_base[rays_off[o]]; count = band_base[rays_off[o + 1]] - band_base[rays_off[o]]; }
   const int lo = start + (int)((long)count * chunk / nchunk), hi = start + (int)((long)count * (chunk + 1) / nchunk);
 
-  // this thread's entries e = tid + 256*u of the row-major upper triangle of the 72x72 matrix
-  int ei[11], ej[11];
-  float acc[11];
-#pragma unroll
-  for (int u = 0; u < 11; ++u) {
-    int e = tid + 256 * u, i = 0;
-    acc[u] = 0.f;
-    if (e < 2628) {
-      while (e >= 72 - i) { e -= 72 - i; ++i; }
-      ei[u] = i; ej[u] = i + e;
-    } else { ei[u] = -1; ej[u] = 0; }
+  // register tiling of the upper triangle of the 72x72 outer product: the 18x18 grid of 4x4 blocks has 171
+  // blocks with bi <= bj; thread t < 171 owns one (two float4 loads and 16 FMAs per row)
+  int bi = 0, bj = 0;
+  const bool worker = tid < 171;
+  if (worker) {
+    int t = tid;
+    while (t >= 18 - bi) { t -= 18 - bi; ++bi; }
+    bj = bi + t;
   }
+  float acc[4][4];
+#pragma unroll
+  for (int r = 0; r < 4; ++r)
+#pragma unroll
+    for (int c = 0; c < 4; ++c) acc[r][c] = 0.f;
   const bool dead = st[o].failed != 0;
   for (int base = lo; base < hi && !dead; base += GN_SLOT) {
     const int nr = min(GN_SLOT, hi - base);
@@ -426,15 +428,28 @@ k_accumulate(const ObjState* __restrict__ st, const int* __restrict__ pts_off,
       J[rr][c] = val;
     }
     __syncthreads();
-    for (int rr = 0; rr < nr; ++rr) {
+    if (worker) {
+      for (int rr = 0; rr < nr; ++rr) {
+        const float4 a4 = *reinterpret_cast<const float4*>(&J[rr][4 * bi]);
+        const float4 b4 = *reinterpret_cast<const float4*>(&J[rr][4 * bj]);
+        const float a[4] = {a4.x, a4.y, a4.z, a4.w}, b[4] = {b4.x, b4.y, b4.z, b4.w};
 #pragma unroll
-      for (int u = 0; u < 11; ++u)
-        if (ei[u] >= 0) acc[u] = fmaf(J[rr][ei[u]], J[rr][ej[u]], acc[u]);
+        for (int r = 0; r < 4; ++r)
+#pragma unroll
+          for (int c = 0; c < 4; ++c) acc[r][c] = fmaf(a[r], b[c], acc[r][c]);
+      }
     }
   }
+  // entry (i, j >= i) of the row-major upper triangle lives at i*72 - i*(i-1)/2 + (j - i)
+  if (worker) {
 #pragma unroll
-  for (int u = 0; u < 11; ++u)
-    if (ei[u] >= 0) out[tid + 256 * u] = acc[u];
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int c = 0; c < 4; ++c) {
+        const int i = 4 * bi + r, j = 4 * bj + c;
+        if (j >= i) out[i * 72 - i * (i - 1) / 2 + (j - i)] = acc[r][c];
+      }
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
