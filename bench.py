@@ -102,7 +102,7 @@ def run_reference(args, rank):
     from qsp_slam_b200 import synth
     import torch
     state = synth.make_decoder_state(0)
-    n_sample = 2
+    n_sample = 8
     cfg, objs = synth.make_workload(WORKLOAD, state, objects=n_sample, pool_size=4096)
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
@@ -251,16 +251,23 @@ def main():
             msk = float(np.mean(tms))
             kern[name] = dict(rows=n, ms=msk, tflops=n * mf * 1e6 / (msk * 1e-3) / 1e12)
         dom = max(kern, key=lambda k: kern[k]["ms"])
+        traffic = None                                    # DRAM bytes per launch of the dominant kernel, from the committed ncu capture
+        try:
+            with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+                traffic = json.load(f)[dom]["dram_bytes"]
+        except Exception:
+            pass
         roof = {"bound": "tensor", "kernel": dom, "achieved": kern[dom]["tflops"], "peak": pk["tflops"],
-                "unit": "TFLOP/s", "frac": kern[dom]["tflops"] / pk["tflops"], "traffic": None,
+                "unit": "TFLOP/s", "frac": kern[dom]["tflops"] / pk["tflops"], "traffic": traffic,
                 "peak_source": pk["source"] + " bf16 burst (kernel timed alone)",
                 "algorithmic_flop_per_row": (FWD_MFLOP if dom == "decoder_fwd" else JAC_MFLOP) * 1e6,
                 "kernels": kern}
         cpu = None
         if not args.no_cpu_baseline:
-            v, dt, th = cpu_port_objects_per_s(state, cfg, objs[:4])
+            ns = min(B, 32)
+            v, dt, th = cpu_port_objects_per_s(state, cfg, objs[:ns])
             cpu = {"value": v, "unit": "objects/s", "cores": th, "kind": "port",
-                   "sample": f"4 of the {B} objects of one step, 10 GN iterations each, oracle port, {dt:.1f} s"}
+                   "sample": f"{ns} of the {B} objects of one step, 10 GN iterations each, oracle port, {dt:.1f} s"}
         out = {"metric": "objects reconstructed/sec (10 GN iters)", "value": value, "unit": "objects/s",
                "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
                "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
