@@ -222,3 +222,15 @@ class MeshExtractor(object):
         voxel_size = 2.0 / (self.voxels_dim - 1)
         vertices, faces = marching_cubes(sdf, 0.0, voxel_size, (-1.0, -1.0, -1.0))
         return ForceKeyErrorDict(vertices=vertices.astype("float32"), faces=faces.astype("int32"))
+
+    def extract_meshes_from_codes(self, codes):
+        """Batch form used by the offline driver (extract_map_objects.py:44-61): the grids of all codes (C,64) are
+        decoded by one kernel launch (BASELINE config 4), then each goes through the isosurface kernels."""
+        from ..mesh import marching_cubes
+        sdf = self.decode_grid(np.asarray(codes, np.float32).reshape(-1, np.asarray(codes).shape[-1]))
+        voxel_size = 2.0 / (self.voxels_dim - 1)
+        out = []
+        for g in sdf:
+            vertices, faces = marching_cubes(g, 0.0, voxel_size, (-1.0, -1.0, -1.0))
+            out.append(ForceKeyErrorDict(vertices=vertices.astype("float32"), faces=faces.astype("int32")))
+        return out

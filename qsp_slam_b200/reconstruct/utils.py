@@ -55,3 +55,9 @@ def create_voxel_grid(vol_dim: int = 128) -> np.ndarray:
     for c in range(3):
         v[:, c] = v[:, c] * np.float32(voxel_size) + np.float32(-1)
     return v
+
+
+def get_decoder(configs):
+    """reconstruct/utils.py:get_decoder - the decoder named by ``configs.DeepSDF_DIR``."""
+    from ..deep_sdf.workspace import config_decoder
+    return config_decoder(configs.DeepSDF_DIR)
