@@ -246,3 +246,58 @@ def test_full_size_properties(dev, decoder_state):
         # the optimiser moves the pose towards the ground truth translation
         assert np.linalg.norm(r.t_cam_obj[:3, 3] - o["t_cam_obj_gt"][:3, 3]) < \
             np.linalg.norm(o["t_cam_obj"][:3, 3] - o["t_cam_obj_gt"][:3, 3]) + 0.05
+
+
+def _decoder_with_env(decoder_state, **env):
+    """The kernel variant is chosen when the handle is created (QSP_TC_PAIR, QSP_TC_T3)."""
+    import os
+    from qsp_slam_b200.decoder import DeviceDecoder
+    old = {k: os.environ.get(k) for k in env}
+    try:
+        for k, v in env.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+        return DeviceDecoder(decoder_state, 0)
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+
+
+def test_cta_pair_kernels_are_bit_identical_to_single_cta(decoder_state):
+    """cta_group::2 changes who streams which half of a weight tile, not the arithmetic: same MMA shapes
+    per row, same accumulation order.  Sizes include ragged tails and an odd tile count (surplus tile of a pair)."""
+    pair = _decoder_with_env(decoder_state, QSP_TC_PAIR="1", QSP_TC_T3=None)
+    single = _decoder_with_env(decoder_state, QSP_TC_PAIR="0", QSP_TC_T3=None)
+    rng = np.random.default_rng(11)
+    z = (rng.standard_normal(64) * 0.1).astype(np.float32)
+    for n in (1, 63, 129, 64 * 149 + 5, 40000):
+        x = synth._ball_points(rng, n)
+        for mode in ("tensor", "fast"):
+            np.testing.assert_array_equal(pair.decode_sdf(z, x, mode=mode), single.decode_sdf(z, x, mode=mode))
+        s1, j1 = pair.decode_sdf_jacobian(z, x, mode="tensor")
+        s0, j0 = single.decode_sdf_jacobian(z, x, mode="tensor")
+        np.testing.assert_array_equal(s1, s0)
+        np.testing.assert_array_equal(j1, j0)
+
+
+def test_three_product_kernel_matches_four_product(decoder_state, orc):
+    """k_decoder_t3 (W_hi*[X_hi|X_lo] + W_lo*X_hi) against k_decoder_tc<TC_SPLIT> and the fp64 oracle."""
+    G, _ = orc
+    t3 = _decoder_with_env(decoder_state, QSP_TC_T3="1")
+    ref = _decoder_with_env(decoder_state, QSP_TC_T3=None)
+    fd64 = G.FoldedDecoder(decoder_state, torch.float64)
+    rng = np.random.default_rng(12)
+    z = (rng.standard_normal(64) * 0.1).astype(np.float32)
+    for n in (1, 65, 3000):
+        x = synth._ball_points(rng, n)
+        s64, g64 = G.decoder_forward_jacobian(fd64, torch.from_numpy(z), torch.from_numpy(x))
+        s3, j3 = t3.decode_sdf_jacobian(z, x, mode="tensor")
+        s4, j4 = ref.decode_sdf_jacobian(z, x, mode="tensor")
+        assert np.abs(s3 - s64.numpy()).max() < 3e-5 and np.abs(s3 - s4).max() < 3e-5
+        assert rows_close(j3[:, :67], g64.numpy(), 2e-4, max_bad_rows=0.02)
+        assert np.abs(t3.decode_sdf(z, x, mode="tensor") - s64.numpy()).max() < 3e-5
