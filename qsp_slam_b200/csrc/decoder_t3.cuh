@@ -108,6 +108,11 @@ k_decoder_t3(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
           const int nt = (s == 15 ? 1 : 4) * tc_step_kblocks(s) * 2;     // (M-tiles) x (K-blocks) x (hi, lo)
           for (int t = 0; t < nt; ++t) {
             mbar_wait(&empty[stage], ph ^ 1);
+            if (g_tc_dbg & 1) {                            // timing experiment: no weight copies (CL == 1 only)
+              mbar_arrive(&full[stage]); src += T3_TILE_BYTES;
+              if (++stage == T3_STAGES) { stage = 0; ph ^= 1; }
+              continue;
+            }
             mbar_expect_tx(&full[stage], T3_TILE_BYTES);
             if (CL > 1) bulk_g2s_mc(sW + stage * T3_TILE_BYTES + poff, src + poff, PIECE, &full[stage], cmask);
             else bulk_g2s(sW + stage * T3_TILE_BYTES, src, T3_TILE_BYTES, &full[stage]);
