@@ -626,7 +626,7 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
   k_fill_obj_map<<<B, 128, 0, st>>>(d_rays_off, B, ray_obj); LAUNCHED();
   k_fill_obj_map<<<B, 128, 0, st>>>(d_pts_off, B, pt_obj); LAUNCHED();
   k_init_state<<<(B + 63) / 64, 64, 0, st>>>(state, in.T, in.codes, B); LAUNCHED();
-  const int ray_blocks = (R * 32 + tb - 1) / tb;
+  const int ray_blocks = std::max(1, (R * 32 + tb - 1) / tb);   // R == 0: every object fails the in-ball test (loss.py:73-74)
   const float* codes_dev = reinterpret_cast<const float*>(state) + offsetof(ObjState, code) / 4;
   const int code_stride = sizeof(ObjState) / 4;
 
@@ -649,7 +649,7 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
     k_exclusive_scan<<<1, 1024, 0, st>>>(band_cnt, band_base, R, counters + 1, M, counters + 2); LAUNCHED();
     k_candidates<true><<<ray_blocks, tb, 0, st>>>(ray_base, R, q_sdf, cand_lim, nullptr, band_base, M, (int)bandcap, q_pts,
                                                   q_code, q_samp, jp_pts, jp_code, row_ray, row_samp, cand_q, counters + 3); LAUNCHED();
-    k_surface_xform<<<(M + tb - 1) / tb, tb, 0, st>>>(state, in.pts, pt_obj, M, jp_pts, jp_code); LAUNCHED();
+    k_surface_xform<<<std::max(1, (M + tb - 1) / tb), tb, 0, st>>>(state, in.pts, pt_obj, M, jp_pts, jp_code); LAUNCHED();
     // (a) SDF + input Jacobian of surface points and candidates (loss.py:34,144), fp32-equivalent
     if ((r = launch_decoder(d, hp_mode, true, jp_pts, jp_code, codes_dev, code_stride, 0, counters + 2, 1, g_sdf, g_jac, st))) return r;
     k_refine_scatter<<<cand_blocks, tb, 0, st>>>(counters + 1, (int)bandcap, cand_q, g_sdf, M, q_sdf); LAUNCHED();
@@ -777,18 +777,18 @@ extern "C" int qsp_estimate_pose_batch(qsp_decoder* d, int32_t num_iterations, i
   GnParamsDev p{};
   k_fill_obj_map<<<B, 128, 0, st>>>(d_pts_off, B, pt_obj); LAUNCHED();
   k_init_pose_only<<<(B + 63) / 64, 64, 0, st>>>(state, in.T, in.scale, in.codes, B); LAUNCHED();
-  k_fill_float<<<(M + tb - 1) / tb, tb, 0, st>>>(row_active, M, 1.f); LAUNCHED();
+  k_fill_float<<<std::max(1, (M + tb - 1) / tb), tb, 0, st>>>(row_active, M, 1.f); LAUNCHED();
   k_count_active<<<(B + 63) / 64, 64, 0, st>>>(d_pts_off, B, m_active); LAUNCHED();
   const float* codes_dev = reinterpret_cast<const float*>(state) + offsetof(ObjState, code) / 4;
   for (int it = 0; it < num_iterations; ++it) {
-    k_surface_xform<<<(M + tb - 1) / tb, tb, 0, st>>>(state, in.pts, pt_obj, M, jp_pts, jp_code); LAUNCHED();
+    k_surface_xform<<<std::max(1, (M + tb - 1) / tb), tb, 0, st>>>(state, in.pts, pt_obj, M, jp_pts, jp_code); LAUNCHED();
     if ((r = launch_decoder(d, d->precision == QSP_PREC_FP32_CORES ? DEC_FP32 : DEC_SPLIT, true, jp_pts, jp_code, codes_dev, sizeof(ObjState) / 4, M, nullptr, 1, g_sdf, g_jac, st))) return r;
     k_accumulate<<<dim3(nchunk, B, 1), 256, 0, st>>>(state, d_pts_off, d_pts_off, nullptr, M, jp_pts, g_sdf, g_jac,
                                                      nullptr, nullptr, 0.f, 0.f, 1, row_active, partials); LAUNCHED();
     k_solve<<<B, 256, 0, st>>>(state, d_pts_off, nchunk, partials, p, 1, m_active, nullptr, nullptr, nullptr); LAUNCHED();
     if (it == 4) {  // optimizer.py:80-82
       CK(cudaMemsetAsync(m_active, 0, (size_t)B * 4, st));
-      k_prune<<<(M + tb - 1) / tb, tb, 0, st>>>(g_sdf, pt_obj, M, row_active, m_active); LAUNCHED();
+      k_prune<<<std::max(1, (M + tb - 1) / tb), tb, 0, st>>>(g_sdf, pt_obj, M, row_active, m_active); LAUNCHED();
     }
   }
   k_finalize_pose_only<<<(B + 63) / 64, 64, 0, st>>>(state, in.scale, B, d_out); LAUNCHED();

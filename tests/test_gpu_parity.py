@@ -301,3 +301,28 @@ def test_three_product_kernel_matches_four_product(decoder_state, orc):
         assert np.abs(s3 - s64.numpy()).max() < 3e-5 and np.abs(s3 - s4).max() < 3e-5
         assert rows_close(j3[:, :67], g64.numpy(), 2e-4, max_bad_rows=0.02)
         assert np.abs(t3.decode_sdf(z, x, mode="tensor") - s64.numpy()).max() < 3e-5
+
+
+def test_empty_inputs_fail_softly(dev, decoder_state):
+    """The reference's convention: numeric failure is `is_good=False`, never an exception - an
+    exception would terminate the SLAM process.  No rays -> fewer than 10 in-ball samples (loss.py:73-74); no surface
+    points -> mean over an empty set is NaN (optimizer.py:168)."""
+    from qsp_slam_b200.reconstruct.optimizer import Optimizer
+    from qsp_slam_b200.reconstruct.utils import ForceKeyErrorDict
+    cfg, objs = synth.make_workload("kitti_single", decoder_state, pool_size=2048, n_surface=64, n_fg=24, n_bg=8,
+                                    samples=20, iters=2)
+    o = objs[0]
+    opt = Optimizer(dev, ForceKeyErrorDict(cfg))
+    e3, e1 = np.zeros((0, 3), np.float32), np.zeros(0, np.float32)
+    assert opt.reconstruct_object(o["t_cam_obj"], o["pts"], o["rays"], o["depth"]).is_good
+    for args in ((o["t_cam_obj"], e3, o["rays"], o["depth"]), (o["t_cam_obj"], o["pts"], e3, e1),
+                 (o["t_cam_obj"], o["pts"][:1], o["rays"][:1], o["depth"][:1])):
+        r = opt.reconstruct_object(*args)
+        assert r.is_good is False and r.t_cam_obj is None and r.code is None
+        float(r.loss)
+    assert opt.reconstruct_object(o["t_cam_obj"], o["pts"], o["rays"], e1).is_good     # all rays background
+    # a batch in which one member has no rays: the others are unaffected
+    good = opt.reconstruct_objects([dict(o), dict(o, rays=e3, depth=e1), dict(o)])
+    assert [g.is_good for g in good] == [True, False, True]
+    np.testing.assert_array_equal(good[0].t_cam_obj, good[2].t_cam_obj)
+    assert dev.decode_sdf(np.zeros(64, np.float32), e3).shape == (0,)
