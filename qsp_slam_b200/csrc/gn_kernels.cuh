@@ -568,28 +568,38 @@ k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
   if (dbg_b && tid < n) dbg_b[o * 71 + tid] = (float)rhs[tid];
   __syncthreads();
   // In-place Cholesky A = L L^T (lower), fp64, with the right-hand side carried as row n of the lower
-  // triangle: after step k, A[n][k] = y_k of L y = b (forward substitution comes for free).
+  // triangle (forward substitution comes for free).  One barrier per column: column k is left UNSCALED in
+  // memory (nothing touches it after step k), every thread applies 1/sqrt(A[k][k]) on the fly, and
+  // rhs[k] keeps that factor, so L_ik = A[i][k] * rhs[k] and y_k = A[n][k] * rhs[k].
   if (tid < n) A[n][tid] = rhs[tid];
   __syncthreads();
-  for (int k = 0; k < n; ++k) {
-    const double dk = sqrt(A[k][k]);
-    if (tid > k && tid <= n) A[tid][k] /= dk;
-    if (tid == 0) rhs[k] = dk;                          // diagonal of L
-    __syncthreads();
-    const int m = n - k;                                // rows k+1..n (n is the rhs row)
-    for (int v = tid; v < m * m; v += blockDim.x) {
-      int i = k + 1 + v / m, j = k + 1 + v % m;
-      if (j <= i && j < n) A[i][j] -= A[i][k] * A[j][k];
+  {
+    const int ti = tid >> 4, tj = tid & 15;               // 16 x 16 threads over the trailing block
+    for (int k = 0; k < n; ++k) {
+      const double inv = 1.0 / sqrt(A[k][k]);
+      if (tid == 0) rhs[k] = inv;
+      const double inv2 = inv * inv;
+      for (int i = k + 1 + ti; i <= n; i += 16) {
+        const double aik = A[i][k] * inv2;
+        const int jmax = i < n ? i : n - 1;
+        for (int j = k + 1 + tj; j <= jmax; j += 16) A[i][j] -= aik * A[j][k];
+      }
+      __syncthreads();
     }
-    __syncthreads();
   }
-  // back substitution L^T x = y, column oriented: x_i = y_i / L_ii, then y_j -= L_ij x_i for j < i
-  for (int i = n - 1; i >= 0; --i) {
-    if (tid == 0) A[n][i] /= rhs[i];
-    __syncthreads();
-    if (tid < i) A[n][tid] -= A[i][tid] * A[n][i];
-    __syncthreads();
+  // back substitution L^T x = y by one warp, column oriented: x_i = y_i / L_ii, then y_j -= L_ij x_i (j < i)
+  if (tid < 32) {
+    for (int j = tid; j < n; j += 32) A[n][j] *= rhs[j];             // y
+    __syncwarp();
+    for (int i = n - 1; i >= 0; --i) {
+      const double xi = A[n][i] * rhs[i];                            // L_ii = 1 / rhs[i]
+      __syncwarp();
+      for (int j = tid; j < i; j += 32) A[n][j] -= (A[i][j] * rhs[j]) * xi;
+      if (tid == 0) A[n][i] = xi;
+      __syncwarp();
+    }
   }
+  __syncthreads();
   if (tid < n) rhs[tid] = A[n][tid];
   __syncthreads();
   if (tid < n) {
