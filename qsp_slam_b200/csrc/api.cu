@@ -606,7 +606,7 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
   ENSURE(d->row_res, rowcap, row_res);
   ENSURE(d->row_ray, rowcap, row_ray);
   ENSURE(d->row_samp, rowcap, row_samp);
-  const int nchunk = std::max(1, std::min(16, 2 * d->num_sms / B));
+  const int nchunk = std::max(1, std::min(64, 2 * d->num_sms / B));
   ENSURE(d->partials, (size_t)B * 2 * nchunk * QSP_PART_STRIDE, partials);
   d_rec = records;
   if (host) ENSURE(d->out_rec, (size_t)B * QSP_RECORD_LEN, d_rec);
@@ -770,7 +770,7 @@ extern "C" int qsp_estimate_pose_batch(qsp_decoder* d, int32_t num_iterations, i
   ENSURE(d->g_jac, (size_t)M * QSP_JSTRIDE, g_jac);
   ENSURE(d->row_active, M, row_active);
   ENSURE(d->m_active, B, m_active);
-  const int nchunk = std::max(1, std::min(16, 2 * d->num_sms / B));
+  const int nchunk = std::max(1, std::min(64, 2 * d->num_sms / B));
   ENSURE(d->partials, (size_t)B * 2 * nchunk * QSP_PART_STRIDE, partials);
   if (host) ENSURE(d->out_rec, (size_t)B * 16, d_out);
   const int tb = 256;

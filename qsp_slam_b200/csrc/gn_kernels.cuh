@@ -403,29 +403,35 @@ k_accumulate(const ObjState* __restrict__ st, const int* __restrict__ pts_off,
   for (int base = lo; base < hi && !dead; base += GN_SLOT) {
     const int nr = min(GN_SLOT, hi - base);
     __syncthreads();
-    // stage [J_pose(7) | J_code(64) | robust residual] for nr rows
-    for (int v = tid; v < nr * 72; v += 256) {
-      int rr = v / 72, c = v - rr * 72, row = base + rr;
-      const float* g = g_jac + (size_t)row * QSP_JSTRIDE;
-      float fac = term == 0 ? 1.f : row_fac[row];
-      if (row_active) fac *= row_active[row];          // pruned surface points (optimizer.py:80-82)
-      float val;
-      if (c >= 7 && c < 71) val = fac * g[c - 7];
-      else if (c == 71) {
-        float r = term == 0 ? g_sdf[row] : row_res[row];
-        val = pose_only ? r : huber_weight(r, term == 0 ? b_sdf : b_render) * r;
-        if (term == 1 && fac == 0.f) val = 0.f;          // candidate row that is not a kept band point
-        if (row_active) val *= row_active[row];
-      } else {
-        float g0 = fac * g[64], g1 = fac * g[65], g2 = fac * g[66];
-        float x = jp_pts[row * 3], y = jp_pts[row * 3 + 1], z = jp_pts[row * 3 + 2];
-        val = c == 0 ? g0 : c == 1 ? g1 : c == 2 ? g2
-            : c == 3 ? g1 * (-z) + g2 * y
-            : c == 4 ? g0 * z + g2 * (-x)
-            : c == 5 ? g0 * (-y) + g1 * x
-                     : g0 * x + g1 * y + g2 * z;
+    // stage [J_pose(7) | J_code(64) | robust residual] for nr rows: 8 threads per row, each loads 8 code
+    // derivatives as two float4 (all loads of a stage are independent: one memory round trip per stage)
+    {
+      const int rr = tid >> 3, part = tid & 7, row = base + rr;
+      if (rr < nr) {
+        const float* g = g_jac + (size_t)row * QSP_JSTRIDE;
+        const float4 g0 = __ldg(reinterpret_cast<const float4*>(g + 8 * part));
+        const float4 g1 = __ldg(reinterpret_cast<const float4*>(g + 8 * part + 4));
+        float fac = term == 0 ? 1.f : row_fac[row];
+        const float act = row_active ? row_active[row] : 1.f;   // pruned surface points (optimizer.py:80-82)
+        if (row_active) fac *= act;
+        float* Jr = &J[rr][7 + 8 * part];
+        Jr[0] = fac * g0.x; Jr[1] = fac * g0.y; Jr[2] = fac * g0.z; Jr[3] = fac * g0.w;
+        Jr[4] = fac * g1.x; Jr[5] = fac * g1.y; Jr[6] = fac * g1.z; Jr[7] = fac * g1.w;
+        if (part == 0) {
+          const float r = term == 0 ? g_sdf[row] : row_res[row];
+          float val = pose_only ? r : huber_weight(r, term == 0 ? b_sdf : b_render) * r;
+          if (term == 1 && fac == 0.f) val = 0.f;          // candidate row that is not a kept band point
+          if (row_active) val *= act;
+          J[rr][71] = val;
+          const float gx = fac * g[64], gy = fac * g[65], gz = fac * g[66];
+          const float x = jp_pts[row * 3], y = jp_pts[row * 3 + 1], z = jp_pts[row * 3 + 2];
+          J[rr][0] = gx; J[rr][1] = gy; J[rr][2] = gz;     // [ I | -[x]x | x ] columns (loss_utils.py:166-185)
+          J[rr][3] = gy * (-z) + gz * y;
+          J[rr][4] = gx * z + gz * (-x);
+          J[rr][5] = gx * (-y) + gy * x;
+          J[rr][6] = gx * x + gy * y + gz * z;
+        }
       }
-      J[rr][c] = val;
     }
     __syncthreads();
     if (worker) {
@@ -515,15 +521,19 @@ k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
   const float ws = pose_only ? 1.f : p.k2, wr = pose_only ? 0.f : p.k1;
   // fixed-order reduction of the chunk partials; entry e of the 72x72 upper triangle
   for (int e = tid; e < 2628; e += blockDim.x) {
-    float ss = 0.f, sr = 0.f;
-    float vs[16], vr[16];                               // all loads in flight first, then a fixed-order sum
+    float ss = 0.f, sr = 0.f;                           // fixed-order sums over the chunks, loads 8 at a time
+    const float* ps = partials + ((size_t)o * 2 + 0) * nchunk * QSP_PART_STRIDE + e;
+    const float* pr = partials + ((size_t)o * 2 + 1) * nchunk * QSP_PART_STRIDE + e;
+    for (int c0 = 0; c0 < nchunk; c0 += 8) {
+      float vs[8], vr[8];
 #pragma unroll
-    for (int c = 0; c < 16; ++c) {
-      vs[c] = c < nchunk ? partials[(((size_t)o * 2 + 0) * nchunk + c) * QSP_PART_STRIDE + e] : 0.f;
-      vr[c] = (c < nchunk && !pose_only) ? partials[(((size_t)o * 2 + 1) * nchunk + c) * QSP_PART_STRIDE + e] : 0.f;
+      for (int c = 0; c < 8; ++c) {
+        vs[c] = c0 + c < nchunk ? ps[(size_t)(c0 + c) * QSP_PART_STRIDE] : 0.f;
+        vr[c] = (c0 + c < nchunk && !pose_only) ? pr[(size_t)(c0 + c) * QSP_PART_STRIDE] : 0.f;
+      }
+#pragma unroll
+      for (int c = 0; c < 8; ++c) { ss += vs[c]; sr += vr[c]; }
     }
-#pragma unroll
-    for (int c = 0; c < 16; ++c) { ss += vs[c]; sr += vr[c]; }
     int i = 0, r = e;
     while (r >= 72 - i) { r -= 72 - i; ++i; }
     int j = i + r;
