@@ -41,6 +41,11 @@
 // timing experiments only (QSP_TC_DEBUG env var at handle creation): bit0 = no weight copies,
 // bit1 = epilogue skips math and stores.  Results are garbage when non-zero.
 __device__ int g_tc_dbg = 0;
+#ifdef TC_PROFILE
+#define TP_MARK(slot) do { long long t_ = clock64(); tp[slot] += t_ - tp_last; tp_last = t_; } while (0)
+#else
+#define TP_MARK(slot) do { } while (0)
+#endif
 
 struct TcDecoderDev {
   const uint8_t* img_fast;                        // forward weight images, fp16(W), consumption order
@@ -230,6 +235,9 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
     constexpr int CW = MODE == TC_SPLIT ? 16 : 32;       // columns this thread owns per 32-column chunk
     uint32_t it = 0;
     uint32_t mask[8][4];
+#ifdef TC_PROFILE
+    long long tp[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tp_last = clock64();   // 0 other, 1 acc_full wait, 2 tmem wait, 3 math, 4 a_free wait, 5 stores, 6 proxy fence, 7 arrive
+#endif
 
     // writes CW consecutive activations (columns colb..) of this thread's row(s) into A'
     auto store_cols = [&](const float* f, int colb, float sc) {
@@ -322,8 +330,10 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
         float psum = 0.f;
         uint32_t mbits[4] = {0u, 0u, 0u, 0u};
         for (int h = 0; h < 2; ++h) {
+          TP_MARK(0);
           mbar_wait(&acc_full[h], par);
           tc_fence_after();
+          TP_MARK(1);
           if (h < nh) {
             // software pipeline: the TMEM load of chunk cc+1 is in flight while chunk cc is processed
             uint32_t vbuf[2][32];
@@ -341,7 +351,9 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
                 }
                 continue;
               }
+              TP_MARK(0);
               tmem_ld_wait();
+              TP_MARK(2);
               if (cc + 1 < NCH) tmem_ld32(tbase + (cc + 1) * (TC_NG * 32), vbuf[(cc + 1) & 1]);
               uint32_t (&v)[32] = vbuf[cc & 1];
               if (dbg & 4) {                               // timing experiment: TMEM reads only
@@ -429,10 +441,16 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
                 }
               }
               if (rewrite) {
+                TP_MARK(3);
                 mbar_wait(&a_free[kb], par);   // this step's MMAs are done with K-block kb
+                TP_MARK(4);
                 if (!(dbg & 8)) store_cols(f, colb, (MODE == TC_SPLIT && fwd) ? TC_SA : 1.f);
                 else if (f[0] == 123.456f) psum += f[CW - 1];
-                { fence_proxy_async(); warp_arrive(&a_ready[kb]); }
+                TP_MARK(5);
+                fence_proxy_async();
+                TP_MARK(6);
+                warp_arrive(&a_ready[kb]);
+                TP_MARK(7);
               }
             }
           }
@@ -484,6 +502,16 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
         }
       }
     }
+#ifdef TC_PROFILE
+    TP_MARK(0);
+    if (blockIdx.x == 0 && (tid == 64 || tid == 64 + 128 + 96)) {
+      long long tot = 0;
+      for (int i = 0; i < 8; ++i) tot += tp[i];
+      printf("k_decoder_tc<%d,%d,%d> tid %d cycles %lld: other %.1f%% acc_full %.1f%% tmem_wait %.1f%% math %.1f%% a_free %.1f%% stores %.1f%% fence %.1f%% arrive %.1f%%\n",
+             MODE, (int)JAC, CG, tid, tot, 100. * tp[0] / tot, 100. * tp[1] / tot, 100. * tp[2] / tot, 100. * tp[3] / tot,
+             100. * tp[4] / tot, 100. * tp[5] / tot, 100. * tp[6] / tot, 100. * tp[7] / tot);
+    }
+#endif
   }
   tc_fence_before();
   __syncthreads();
