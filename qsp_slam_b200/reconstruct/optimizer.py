@@ -73,9 +73,15 @@ class Optimizer(object):
         """Batch of independent detections; each is a mapping with ``t_cam_obj`` (4,4), ``pts`` (M,3),
         ``rays`` (N,3), ``depth`` (K,) (the fields of the reference's per-detection objects,
         reconstruct_frame.py:48-57).  One result per detection, in order."""
-        B = len(detections)
-        if B == 0:
+        if len(detections) == 0:
             return []
+        rec = self.reconstruct_objects_records(detections, codes)
+        return [self._result(rec[i]) for i in range(rec.shape[0])]
+
+    def reconstruct_objects_records(self, detections: Sequence[dict], codes: Optional[Sequence] = None) -> np.ndarray:
+        """Same solve, results as the raw (B,82) records (t_cam_obj 16 | code 64 | is_good | loss) that the
+        multi-GPU all-gather moves (sharding.gather_records)."""
+        B = len(detections)
         T = np.stack([N.f32(d["t_cam_obj"]).reshape(16) for d in detections])
         pts, pts_off = self._pack([N.f32(d["pts"]) for d in detections], 3)
         rays, rays_off = self._pack([N.f32(d["rays"]).reshape(-1, 3) for d in detections], 3)
@@ -92,7 +98,7 @@ class Optimizer(object):
         N.check(N.lib().qsp_reconstruct_batch(self.decoder.handle, C.byref(prm), B, N.ptr(T), N.ptr(z),
                                               N.ptr(pts), N.i32p(pts_off), N.ptr(rays), N.i32p(rays_off),
                                               N.ptr(depth), N.i32p(depth_off), N.ptr(rec), N.FLAG_HOST_PTRS, None))
-        return [self._result(rec[i]) for i in range(B)]
+        return rec
 
     def pack(self, detections: Sequence[dict]):
         """Concatenated arrays + offsets of a detection list (the layout the C ABI takes)."""
