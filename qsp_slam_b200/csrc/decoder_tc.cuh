@@ -131,7 +131,7 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
     // arrivals are one elected lane per warp; the leader's barriers also count the peer CTA's warps
     for (int i = 0; i < NST; ++i) { mbar_init(&full[i], (CG == 2 && leader) ? 2 : 1); mbar_init(&empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&acc_full[i], 1); mbar_init(&acc_free[i], CG * (TC_EPI / 32)); }
-    for (int i = 0; i < 8; ++i) { mbar_init(&a_ready[i], CG * (TC_EPI / 32)); mbar_init(&a_free[i], 1); }
+    for (int i = 0; i < 8; ++i) { mbar_init(&a_ready[i], CG * 4); mbar_init(&a_free[i], 1); }
     fence_mbar_init();
   }
   if (warp == 1) { if (CG == 2) tmem_alloc2(tmem_slot, 512); else tmem_alloc(tmem_slot, 512); }
@@ -236,7 +236,7 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
     uint32_t it = 0;
     uint32_t mask[8][4];
 #ifdef TC_PROFILE
-    long long tp[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tp_last = clock64();   // 0 other, 1 acc_full wait, 2 tmem wait, 3 math, 4 a_free wait, 5 stores, 6 proxy fence, 7 arrive
+    long long tp[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, tp_last = clock64();   // 0 other, 1 acc_full wait, 2 tmem wait, 3 math, 4 a_free wait, 5 stores, 6 proxy fence, 7 arrive, 8 bias staging, 9 tanh head + seed, 10 tile staging, 11 end of half
 #endif
 
     // writes CW consecutive activations (columns colb..) of this thread's row(s) into A'
@@ -273,46 +273,54 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
       const bool valid = grow < n;
       const float* my_code = (code_idx && valid) ? codes + (size_t)code_idx[grow] * code_stride : pass_code;
       // ---- stage the input rows [code, xyz, 0...] into K-blocks 0,1 (loss_utils.py:71-72) ----
-      // chunk cc of group g covers columns (cc*TC_NG + g)*32 of a half, so all warps finish K-block 4h+cc together; group 0 stages K-blocks 0 and 1 here.
+      // Group g owns K-blocks {g, g+2} of each accumulator half (two 32-column chunks each), so K-blocks 4h, 4h+1
+      // are rewritten after half of a half's epilogue and 4h+2, 4h+3 at its end - the order the next layer's MMAs
+      // consume them.  Staging: group 0 writes K-block 0 (the code), group 1 K-block 1 (xyz, zero padding); every
+      // load of a thread is issued before the first use (one memory round trip per tile).
       {
+        static_assert(TC_NG == 2, "the epilogue mapping below is written for two warp groups");
         const uint32_t prev = (it & 1) ^ 1;              // the previous step's MMAs released the K-blocks
 #pragma unroll
-        for (int u = 0; u < 8; ++u) mbar_wait(&a_free[u], prev);
-        if (g * KPG < 2) {                               // the groups that own K-blocks 0 and 1
+        for (int u = 0; u < 4; ++u) mbar_wait(&a_free[(u >> 1) * 4 + (u & 1) * 2 + g], prev);
+        {
           const int rr = e & 127;                        // A' row 0..127
           const int ip = MODE == TC_SPLIT ? (rr >> 1) : rr;
           const long r = tile * ROWS + ip;
           const bool ok = r < n;
-          const float* cz = (code_idx && ok) ? codes + (size_t)code_idx[r] * code_stride : pass_code;
-#pragma unroll 1
-          for (int c8 = 0; c8 < 8 * KPG; ++c8) {
-            const int col = g * KPG * 64 + c8 * 8;
+          float4 cv[16];
+          if (g == 0) {
+            const float4* cz = reinterpret_cast<const float4*>((code_idx && ok) ? codes + (size_t)code_idx[r] * code_stride : pass_code);
+#pragma unroll
+            for (int u = 0; u < 16; ++u) cv[u] = ok ? __ldg(cz + u) : make_float4(0.f, 0.f, 0.f, 0.f);
+          } else {
+#pragma unroll
+            for (int u = 0; u < 16; ++u) cv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (ok) cv[0] = make_float4(pts[r * 3], pts[r * 3 + 1], pts[r * 3 + 2], 0.f);
+          }
+#pragma unroll
+          for (int c8 = 0; c8 < 8; ++c8) {
+            const float v[8] = {cv[2 * c8].x, cv[2 * c8].y, cv[2 * c8].z, cv[2 * c8].w,
+                                cv[2 * c8 + 1].x, cv[2 * c8 + 1].y, cv[2 * c8 + 1].z, cv[2 * c8 + 1].w};
             uint32_t w[4];
 #pragma unroll
             for (int j = 0; j < 4; ++j) {
-              float v2[2];
-#pragma unroll
-              for (int u = 0; u < 2; ++u) {
-                const int c = col + 2 * j + u;
-                v2[u] = !ok ? 0.f : c < QSP_CODE ? cz[c] : c < QSP_IN ? pts[r * 3 + (c - QSP_CODE)] : 0.f;
-              }
               if (MODE == TC_SPLIT) {
                 uint32_t hi, lo;
-                split2(v2[0] * TC_SA, v2[1] * TC_SA, hi, lo);
+                split2(v[2 * j] * TC_SA, v[2 * j + 1] * TC_SA, hi, lo);
                 w[j] = (rr & 1) ? lo : hi;
               } else {
-                w[j] = pack_h2(v2[0], v2[1]);
+                w[j] = pack_h2(v[2 * j], v[2 * j + 1]);
               }
             }
-            *reinterpret_cast<uint4*>(sA + (col >> 6) * TC_ABLK_BYTES + sw128_offset(rr, (col & 63) >> 3)) =
-                make_uint4(w[0], w[1], w[2], w[3]);
+            *reinterpret_cast<uint4*>(sA + g * TC_ABLK_BYTES + sw128_offset(rr, c8)) = make_uint4(w[0], w[1], w[2], w[3]);
           }
           fence_proxy_async();
         }
 #pragma unroll
-        for (int u = 0; u < 8; ++u) warp_arrive(&a_ready[u]);
+        for (int u = 0; u < 4; ++u) warp_arrive(&a_ready[(u >> 1) * 4 + (u & 1) * 2 + g]);
       }
       float sdf_v = 0.f;
+      TP_MARK(10);
 
       for (int s = 0; s < NSTEPS; ++s, ++it) {
         const uint32_t par = it & 1;
@@ -322,9 +330,11 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
         const bool last = s + 1 == NSTEPS;
         const bool rewrite = !(fwd && l == 7) && !last;
         if (fwd) {                                       // bias of this layer -> smem (all epilogue threads)
+          TP_MARK(0);
           asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI) : "memory");
           if (e < 256) *reinterpret_cast<float2*>(sbias + 2 * e) = __ldg(reinterpret_cast<const float2*>(dw.bias + l * QSP_HID + 2 * e));
           asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI) : "memory");
+          TP_MARK(8);
         }
         if (s == 15) asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI) : "memory");   // skip-gradient writes of step 11 are read below
         float psum = 0.f;
@@ -337,30 +347,30 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
           if (h < nh) {
             // software pipeline: the TMEM load of chunk cc+1 is in flight while chunk cc is processed
             uint32_t vbuf[2][32];
-            const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + h * 256 + g * 32;
+            const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + h * 256 + g * 64;   // + (cc>>1)*128 + (cc&1)*32
             if (!(dbg & 2)) tmem_ld32(tbase, vbuf[0]);
 #pragma unroll
             for (int cc = 0; cc < NCH; ++cc) {
-              const int col0 = h * 256 + (cc * TC_NG + g) * 32;
+              const int col0 = h * 256 + ((cc >> 1) * 2 + g) * 64 + (cc & 1) * 32;
               const int kb = col0 >> 6;
               const int bit0 = (h * NCH + cc) * CW;
               if (dbg & 2) {
                 if (rewrite) {
-                  mbar_wait(&a_free[kb], par);
-                  { fence_proxy_async(); warp_arrive(&a_ready[kb]); }
+                  if ((cc & 1) == 0) mbar_wait(&a_free[kb], par);
+                  if (cc & 1) { fence_proxy_async(); warp_arrive(&a_ready[kb]); }
                 }
                 continue;
               }
               TP_MARK(0);
               tmem_ld_wait();
               TP_MARK(2);
-              if (cc + 1 < NCH) tmem_ld32(tbase + (cc + 1) * (TC_NG * 32), vbuf[(cc + 1) & 1]);
+              if (cc + 1 < NCH) tmem_ld32(tbase + ((cc + 1) >> 1) * 128 + ((cc + 1) & 1) * 32, vbuf[(cc + 1) & 1]);
               uint32_t (&v)[32] = vbuf[cc & 1];
               if (dbg & 4) {                               // timing experiment: TMEM reads only
                 if (v[0] == 0x7fc12345u && v[31] == 0x7fc54321u) psum += 1.f;
                 if (rewrite) {
-                  mbar_wait(&a_free[kb], par);
-                  { fence_proxy_async(); warp_arrive(&a_ready[kb]); }
+                  if ((cc & 1) == 0) mbar_wait(&a_free[kb], par);
+                  if (cc & 1) { fence_proxy_async(); warp_arrive(&a_ready[kb]); }
                 }
                 continue;
               }
@@ -442,25 +452,28 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
               }
               if (rewrite) {
                 TP_MARK(3);
-                mbar_wait(&a_free[kb], par);   // this step's MMAs are done with K-block kb
+                if ((cc & 1) == 0) mbar_wait(&a_free[kb], par);   // this step's MMAs are done with K-block kb
                 TP_MARK(4);
                 if (!(dbg & 8)) store_cols(f, colb, (MODE == TC_SPLIT && fwd) ? TC_SA : 1.f);
                 else if (f[0] == 123.456f) psum += f[CW - 1];
                 TP_MARK(5);
-                fence_proxy_async();
+                if (cc & 1) fence_proxy_async();
                 TP_MARK(6);
-                warp_arrive(&a_ready[kb]);
+                if (cc & 1) warp_arrive(&a_ready[kb]);
                 TP_MARK(7);
               }
             }
           }
           tc_fence_before();
+          TP_MARK(0);
           warp_arrive(&acc_free[h]);
+          TP_MARK(11);
         }
         if (JAC && fwd) {
 #pragma unroll
           for (int u = 0; u < 4; ++u) mask[l][u] = mbits[u];
         }
+        TP_MARK(0);
         if (fwd && l == 7) {
           // ---- tanh head (deep_sdf_decoder.py:107-108): combine the partial dot products ----
           if (MODE == TC_SPLIT) psum += __shfl_xor_sync(0xffffffffu, psum, 1);
@@ -480,7 +493,7 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
 #pragma unroll 1
             for (int c8 = 0; c8 < 2 * NCH; ++c8) {
               const int h = c8 / NCH, cc = c8 % NCH;
-              const int col0 = h * 256 + (cc * TC_NG + g) * 32, kb = col0 >> 6;
+              const int col0 = h * 256 + ((cc >> 1) * 2 + g) * 64 + (cc & 1) * 32, kb = col0 >> 6;
               const int colb = col0 + (odd ? 16 : 0), bit0 = (h * NCH + cc) * 16;
               float gsd[16];
 #pragma unroll
@@ -494,22 +507,24 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
                   gsd[j] = keep ? d * ww[u] : 0.f;
                 }
               }
-              mbar_wait(&a_free[kb], par);
+              if ((cc & 1) == 0) mbar_wait(&a_free[kb], par);
               store_cols(gsd, colb, 1.f);
-              { fence_proxy_async(); warp_arrive(&a_ready[kb]); }
+              if (cc & 1) { fence_proxy_async(); warp_arrive(&a_ready[kb]); }
             }
           }
         }
+        TP_MARK(9);
       }
     }
 #ifdef TC_PROFILE
     TP_MARK(0);
     if (blockIdx.x == 0 && (tid == 64 || tid == 64 + 128 + 96)) {
       long long tot = 0;
-      for (int i = 0; i < 8; ++i) tot += tp[i];
-      printf("k_decoder_tc<%d,%d,%d> tid %d cycles %lld: other %.1f%% acc_full %.1f%% tmem_wait %.1f%% math %.1f%% a_free %.1f%% stores %.1f%% fence %.1f%% arrive %.1f%%\n",
+      for (int i = 0; i < 12; ++i) tot += tp[i];
+      printf("k_decoder_tc<%d,%d,%d> tid %d cycles %lld: other %.1f%% acc_full %.1f%% tmem_wait %.1f%% math %.1f%% a_free %.1f%% stores %.1f%% fence %.1f%% arrive %.1f%% bias %.1f%% head+seed %.1f%% tile staging %.1f%% acc_free arrive %.1f%%\n",
              MODE, (int)JAC, CG, tid, tot, 100. * tp[0] / tot, 100. * tp[1] / tot, 100. * tp[2] / tot, 100. * tp[3] / tot,
-             100. * tp[4] / tot, 100. * tp[5] / tot, 100. * tp[6] / tot, 100. * tp[7] / tot);
+             100. * tp[4] / tot, 100. * tp[5] / tot, 100. * tp[6] / tot, 100. * tp[7] / tot, 100. * tp[8] / tot, 100. * tp[9] / tot,
+             100. * tp[10] / tot, 100. * tp[11] / tot);
     }
 #endif
   }
