@@ -12,6 +12,7 @@
 #include "decoder_ffma.cuh"
 #include "decoder_tc.cuh"
 #include "decoder_t3.cuh"
+#include "decoder_p3.cuh"
 #include "gn_kernels.cuh"
 #include "mesh_kernels.cuh"
 
@@ -61,6 +62,7 @@ struct qsp_decoder {
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   float last_ms = 0.f;
   bool t3 = false;
+  bool p3 = true;                                  // three-product CTA-pair kernel for the fp16-pair evaluations
   bool pair = true;                                // CTA pairs (cta_group::2) for k_decoder_tc
   int pair_grid = 148;
   int cluster = 2;                                 // CTAs per cluster sharing a multicast weight stream
@@ -257,7 +259,10 @@ extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_
   CK(cudaFuncSetAttribute(k_decoder_tc<TC_FAST, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
   CK(cudaFuncSetAttribute(k_decoder_tc<TC_SPLIT, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
   CK(cudaFuncSetAttribute(k_decoder_tc<TC_SPLIT, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+  CK(cudaFuncSetAttribute(k_decoder_p3<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+  CK(cudaFuncSetAttribute(k_decoder_p3<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
   if (const char* e2 = getenv("QSP_TC_PAIR")) d->pair = atoi(e2) != 0;
+  if (const char* e3 = getenv("QSP_TC_P3")) d->p3 = atoi(e3) != 0;       // three-product CTA-pair kernel k_decoder_p3
   d->t3 = getenv("QSP_TC_T3") != nullptr;             // A/B switch: the transposed three-product kernel k_decoder_t3
   {
     cudaLaunchConfig_t cfg = {};
@@ -405,7 +410,13 @@ static int launch_decoder(qsp_decoder* d, int mode, bool jac, const float* pts, 
   } while (0)
     if (mode == DEC_FAST && !jac)
       TC_LAUNCH(TC_FAST, false);
-    else if (d->t3) {
+    else if (d->p3 && d->pair) {
+      int r_ = jac ? launch_clustered(k_decoder_p3<true>, std::min<int>(grid.x, d->pair_grid), 2, TC_SMEM_BYTES, st, d->tc, pts, code_idx,
+                                      codes, code_stride, n_codes_y, n, n_dev, sdf, jacp)
+                   : launch_clustered(k_decoder_p3<false>, std::min<int>(grid.x, d->pair_grid), 2, TC_SMEM_BYTES, st, d->tc, pts, code_idx,
+                                      codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
+      if (r_) return r_;
+    } else if (d->t3) {
       int r = launch_t3(d, jac, grid.x, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp, st);
       if (r) return r;
     }

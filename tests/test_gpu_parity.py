@@ -271,8 +271,8 @@ def _decoder_with_env(decoder_state, **env):
 def test_cta_pair_kernels_are_bit_identical_to_single_cta(decoder_state):
     """cta_group::2 changes who streams which half of a weight tile, not the arithmetic: same MMA shapes
     per row, same accumulation order.  Sizes include ragged tails and an odd tile count (surplus tile of a pair)."""
-    pair = _decoder_with_env(decoder_state, QSP_TC_PAIR="1", QSP_TC_T3=None)
-    single = _decoder_with_env(decoder_state, QSP_TC_PAIR="0", QSP_TC_T3=None)
+    pair = _decoder_with_env(decoder_state, QSP_TC_PAIR="1", QSP_TC_P3="0", QSP_TC_T3=None)
+    single = _decoder_with_env(decoder_state, QSP_TC_PAIR="0", QSP_TC_P3="0", QSP_TC_T3=None)
     rng = np.random.default_rng(11)
     z = (rng.standard_normal(64) * 0.1).astype(np.float32)
     for n in (1, 63, 129, 64 * 149 + 5, 40000):
@@ -288,8 +288,8 @@ def test_cta_pair_kernels_are_bit_identical_to_single_cta(decoder_state):
 def test_three_product_kernel_matches_four_product(decoder_state, orc):
     """k_decoder_t3 (W_hi*[X_hi|X_lo] + W_lo*X_hi) against k_decoder_tc<TC_SPLIT> and the fp64 oracle."""
     G, _ = orc
-    t3 = _decoder_with_env(decoder_state, QSP_TC_T3="1")
-    ref = _decoder_with_env(decoder_state, QSP_TC_T3=None)
+    t3 = _decoder_with_env(decoder_state, QSP_TC_T3="1", QSP_TC_P3="0")
+    ref = _decoder_with_env(decoder_state, QSP_TC_T3=None, QSP_TC_P3="0")
     fd64 = G.FoldedDecoder(decoder_state, torch.float64)
     rng = np.random.default_rng(12)
     z = (rng.standard_normal(64) * 0.1).astype(np.float32)
@@ -326,3 +326,34 @@ def test_empty_inputs_fail_softly(dev, decoder_state):
     assert [g.is_good for g in good] == [True, False, True]
     np.testing.assert_array_equal(good[0].t_cam_obj, good[2].t_cam_obj)
     assert dev.decode_sdf(np.zeros(64, np.float32), e3).shape == (0,)
+
+
+
+def test_three_product_pair_kernel_vs_fp64_oracle(decoder_state, orc):
+    """k_decoder_p3 (the default fp16-pair kernel: M = 128 CTA-pair MMAs, X_hi*W_hi + X_lo*W_hi + X_hi*W_lo with the small
+    terms in their own accumulator) against the fp64 oracle, and against the four-product kernel it replaces: it must
+    be at least as accurate.  Ragged sizes, an odd number of tiles (surplus tile of a pair), several codes."""
+    G, _ = orc
+    p3 = _decoder_with_env(decoder_state, QSP_TC_P3="1", QSP_TC_T3=None)
+    p4 = _decoder_with_env(decoder_state, QSP_TC_P3="0", QSP_TC_T3=None)
+    fd64 = G.FoldedDecoder(decoder_state, torch.float64)
+    rng = np.random.default_rng(13)
+    z = (rng.standard_normal(64) * 0.1).astype(np.float32)
+    for n in (1, 63, 65, 64 * 149 + 5, 20000):
+        x = synth._ball_points(rng, n)
+        s64, g64 = G.decoder_forward_jacobian(fd64, torch.from_numpy(z), torch.from_numpy(x))
+        s64, g64 = s64.numpy(), g64.numpy()
+        s3, j3 = p3.decode_sdf_jacobian(z, x, mode="tensor")
+        s4, j4 = p4.decode_sdf_jacobian(z, x, mode="tensor")
+        e3, e4 = np.abs(s3 - s64).max(), np.abs(s4 - s64).max()
+        assert e3 < 1e-5 and e3 <= e4 + 1e-6, (n, e3, e4)
+        assert rows_close(j3, g64, 1e-4, max_bad_rows=0.01)
+        r3 = np.median(np.abs(j3 - g64).max(1)); r4 = np.median(np.abs(j4 - g64).max(1))
+        assert r3 <= r4 * 1.1 + 1e-7, (n, r3, r4)
+        assert np.abs(p3.decode_sdf(z, x, mode="tensor") - s64).max() < 1e-5
+    codes = (rng.standard_normal((3, 64)) * 0.1).astype(np.float32)
+    x = synth._ball_points(rng, 700)
+    got = p3.decode_sdf(codes, x, mode="tensor").reshape(3, -1)
+    for c in range(3):
+        ref = G.decode_sdf(fd64, torch.from_numpy(codes[c]), torch.from_numpy(x)).numpy()
+        assert np.abs(got[c] - ref).max() < 1e-5
