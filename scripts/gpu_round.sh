@@ -10,6 +10,6 @@ tail -c 3000 gpurun_out/bench.json
 timeout 600 python scripts/profile_decoder.py 383888 115844 > gpurun_out/profile_decoder.log 2>&1; echo "profile_decoder rc=$?"; cat gpurun_out/profile_decoder.log
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches.csv \
   python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_bench.log 2>&1; echo "ncu launches rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_decoder_tc -c 4 -o gpurun_out/decoder_tc -f \
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_decoder_ -c 4 -o gpurun_out/decoder_tc -f \
   python scripts/profile_decoder.py 383888 115844 > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?"
 ls -la gpurun_out
