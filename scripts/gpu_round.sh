@@ -12,4 +12,5 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --c
   python bench.py --steps 2 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_bench.log 2>&1; echo "ncu launches rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_decoder_ -c 4 -o gpurun_out/decoder_tc -f \
   python scripts/profile_decoder.py 383888 115844 > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?"
+timeout 400 python scripts/bench_configs.py > gpurun_out/configs.jsonl 2> gpurun_out/configs.err; echo "configs rc=$?"
 ls -la gpurun_out
