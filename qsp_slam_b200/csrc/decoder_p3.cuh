@@ -51,7 +51,10 @@ k_decoder_p3(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
   const long n = n_dev ? (long)(*n_dev) : n_host;
   const long ntiles = (n + P3_PTS - 1) / P3_PTS;
   const long total_tiles = ntiles * n_codes;
-  const long iters = (total_tiles + gridDim.x - 1) / gridDim.x;   // both CTAs of a pair walk the same number of tiles
+  // tiles this CTA walks: tile i*gridDim.x + blockIdx.x; both CTAs of a pair walk the same number (a surplus tile has
+  // no valid rows), and a pair whose tiles are all beyond the end retires so that the next kernel's CTAs can start
+  const long pair_first = (long)(blockIdx.x & ~1u);
+  const long iters = pair_first < total_tiles ? (total_tiles - pair_first + gridDim.x - 1) / gridDim.x : 0;
   const uint32_t crank = cluster_ctarank();
   const bool leader = crank == 0;
 

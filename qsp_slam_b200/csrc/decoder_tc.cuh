@@ -122,7 +122,10 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
   const long ntiles = (n + ROWS - 1) / ROWS;
   const long total_tiles = ntiles * n_codes;
   // both CTAs of a pair walk the same number of tiles; a surplus tile has no valid rows
-  const long iters = (total_tiles + gridDim.x - 1) / gridDim.x;
+  // tiles this CTA walks: tile i*gridDim.x + blockIdx.x; both CTAs of a pair walk the same number (a surplus tile has
+  // no valid rows), and a pair whose tiles are all beyond the end retires so that the next kernel's CTAs can start
+  const long pair_first = (long)(blockIdx.x & ~(unsigned)(CG - 1));
+  const long iters = pair_first < total_tiles ? (total_tiles - pair_first + gridDim.x - 1) / gridDim.x : 0;
   const uint32_t crank = CG == 2 ? cluster_ctarank() : 0;
   const bool leader = crank == 0;
 

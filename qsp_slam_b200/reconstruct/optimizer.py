@@ -110,7 +110,7 @@ class Optimizer(object):
             depth = np.zeros(1, np.float32)
         return dict(T=T, pts=pts, pts_off=pts_off, rays=rays, rays_off=rays_off, depth=depth, depth_off=depth_off)
 
-    def reconstruct_packed_device(self, packed: dict, records, codes=None, sync: bool = True):
+    def reconstruct_packed_device(self, packed: dict, records, codes=None, sync: bool = True, stream=None):
         """Same solve with inputs already resident in HBM: ``packed`` holds torch CUDA tensors for
         T/pts/rays/depth and host int32 numpy offsets; ``records`` (B,82) CUDA tensor is written."""
         B = packed["T"].shape[0]
@@ -119,7 +119,8 @@ class Optimizer(object):
                                               N.ptr(packed["pts"]), N.i32p(packed["pts_off"]), N.ptr(packed["rays"]),
                                               N.i32p(packed["rays_off"]), N.ptr(packed["depth"]),
                                               N.i32p(packed["depth_off"]), N.ptr(records),
-                                              N.FLAG_SYNC if sync else 0, None))
+                                              N.FLAG_SYNC if sync else 0,
+                                              None if stream is None else C.c_void_p(int(stream))))
         return records
 
     @staticmethod
