@@ -118,9 +118,11 @@ def test_one_gn_iteration_vs_reference_and_oracle(golden, dev, orc, name, style,
     assert out.is_good
     # Tolerances.  fp32: 1e-3 relative on pose and code (north_star).  tensor: the SDF of a surface
     # point is itself the residual (|s| ~ 1e-2), and the tensor pipe's fp32 accumulation leaves an
-    # absolute SDF error of ~5e-6 (vs 1.5e-6 for sequential fp32 FMAs), i.e. ~1e-3 relative on b; the
-    # pose stays within 1e-3, the weakly constrained code (k3 regulariser only) within 5e-3.
-    tol_code, tol_b, tol_dx = (1e-3, 1e-3, 2e-3) if precision == "fp32" else (5e-3, 5e-3, 5e-3)
+    # absolute SDF error of ~3e-6 (vs 1.5e-6 for sequential fp32 FMAs), i.e. a few 1e-4 relative on b; the
+    # pose stays within 1e-3, the weakly constrained code (k3 regulariser only) within 3e-3.
+    # Observed (scripts/parity_margins.py, three-product kernel): tensor pose <= 1.2e-5, code <= 1.7e-3, b <= 5.3e-4,
+    # dx <= 2.2e-3 (kitti1: its H amplifies the 2e-4 error of b ten-fold); fp32 code <= 4.9e-4, dx <= 1.1e-3.
+    tol_code, tol_b, tol_dx = (1e-3, 1e-3, 2e-3) if precision == "fp32" else (3e-3, 1e-3, 3e-3)
     # (1) against the unmodified reference's own output
     t_ref, c_ref = golden[p + "it1_t"], golden[p + "it1_code"]
     assert np.abs(out.t_cam_obj - t_ref).max() < 1e-3 * np.abs(t_ref).max()
