@@ -686,7 +686,8 @@ __global__ void k_finalize_pose_only(const ObjState* __restrict__ st, const floa
 // candidate rows: in-ball samples whose first-pass SDF lies within +-lim of zero (lim = th + margin
 // when the first pass is the single-pass fp16 kernel, lim = th when it is exact).  They are
 // re-evaluated, with the input Jacobian, by the fp32-equivalent kernel; every true band point
-// (loss.py:88) is among them as long as the first-pass error stays below the margin.
+// (loss.py:88) that can pass the de_do test is among them as long as the first-pass error stays below the
+// margin; samples behind a ray's first certainly-opaque sample are left out (see below).
 // Order: (ray, sample) ascending, i.e. the order torch.where gives (loss.py:68,89-90).
 // ------------------------------------------------------------------------------------------------
 template <bool FILL>
@@ -703,8 +704,13 @@ __global__ void k_candidates(const int* __restrict__ ray_base, int R, const floa
   const int base = FILL ? cand_base[r] : 0;
   for (int i0 = lo; i0 < hi; i0 += 32) {
     int i = i0 + lane;
-    bool c = false;
-    if (i < hi) { float s = q_sdf[i]; c = (s > -lim) && (s < lim); }
+    bool c = false, opq = false;
+    if (i < hi) { float s = q_sdf[i]; c = (s > -lim) && (s < lim); opq = s <= -lim; }
+    // Behind the first sample that is certainly opaque (exact s <= -th, occupancy exactly 1) the transmittance is
+    // exactly 0: such samples contribute nothing to the rendered depth and their de_do is 0, so they can never be
+    // kept (loss.py:99,118-125).  They need neither the exact SDF nor a Jacobian row.
+    const unsigned mo = __ballot_sync(0xffffffffu, opq);
+    if (mo) c = c && lane < __ffs(mo) - 1;
     unsigned m = __ballot_sync(0xffffffffu, c);
     if (FILL && c) {
       int k = base + cnt + __popc(m & ((1u << lane) - 1u));
@@ -720,6 +726,7 @@ __global__ void k_candidates(const int* __restrict__ ray_base, int R, const floa
       }
     }
     cnt += __popc(m);
+    if (mo) break;
   }
   if (!FILL && lane == 0) cand_cnt[r] = cnt;
 }

@@ -135,7 +135,11 @@ def test_one_gn_iteration_vs_reference_and_oracle(golden, dev, orc, name, style,
                        torch.from_numpy(golden[p + "rays"]), torch.from_numpy(golden[p + "depth"]))
     ren = o["render"]
     assert it["n_inball"] == ren["valid_ray"].shape[0]
-    assert it["n_band"] == ren["band_ray"].shape[0]
+    # n_band is a diagnostic: band samples behind a ray's first opaque sample never get the exact SDF in the product
+    # path (they cannot be kept, k_candidates), so there it is counted on the first-pass value - it can differ from
+    # the reference count only by samples whose |s| is within the first-pass margin of th
+    near = int(((ren["sdf"].abs() - prm.th).abs() < 0.006).sum())
+    assert abs(it["n_band"] - ren["band_ray"].shape[0]) <= (0 if precision == "fp32" else near)
     assert it["n_keep"] == ren["keep_ray"].shape[0]
     assert np.array_equal(it["keep_ray"], ren["keep_ray"].numpy())
     assert np.array_equal(it["keep_sample"], ren["keep_sample"].numpy())
