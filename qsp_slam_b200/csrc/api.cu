@@ -52,7 +52,7 @@ struct qsp_decoder {
   Buf in_T, in_code, in_pts, in_rays, in_depth, in_scale, out_rec;
   Buf pts_off, rays_off, depth_off, ray_obj, pt_obj;
   Buf state, counters, ray_cnt, ray_base, band_cnt, band_base;
-  Buf q_pts, q_code, q_samp, cand_q, q_sdf, slot, ray_res;
+  Buf q_pts, q_code, q_samp, cand_q, q_sdf, slot, ray_res, ray_nev, ph_list, ph_code;
   Buf jp_pts, jp_code, g_sdf, g_jac, row_fac, row_res, row_ray, row_samp, row_active, m_active;
   Buf partials, dbgH, dbgb, dbgdx;
   Buf dec_pts, dec_codes, dec_out, dec_jac;
@@ -67,6 +67,7 @@ struct qsp_decoder {
   int pair_grid = 148;
   int cluster = 2;                                 // CTAs per cluster sharing a multicast weight stream
   int t3_grid = 148;
+  bool phases = true;                              // first pass front to back in phases of 32 samples per ray
 };
 
 template <typename T>
@@ -304,6 +305,7 @@ extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_
   }
   CK(cudaFuncSetAttribute(k_decoder_ffma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FF_SMEM_BYTES));
   CK(cudaFuncSetAttribute(k_decoder_ffma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FF_SMEM_BYTES));
+  if (const char* e = getenv("QSP_PHASES")) d->phases = atoi(e) != 0;
   if (const char* dbg_env = getenv("QSP_TC_DEBUG")) {
     int v = atoi(dbg_env);
     CK(cudaMemcpyToSymbol(g_tc_dbg, &v, sizeof(int)));
@@ -323,7 +325,8 @@ extern "C" void qsp_decoder_destroy(qsp_decoder* d) {
                  &d->ray_cnt, &d->ray_base, &d->band_cnt, &d->band_base, &d->q_pts, &d->q_code, &d->q_samp, &d->cand_q, &d->q_sdf,
                  &d->slot, &d->ray_res, &d->jp_pts, &d->jp_code, &d->g_sdf, &d->g_jac, &d->row_fac,
                  &d->row_res, &d->row_ray, &d->row_samp, &d->row_active, &d->m_active, &d->partials,
-                 &d->dbgH, &d->dbgb, &d->dbgdx, &d->dec_pts, &d->dec_codes, &d->dec_out, &d->dec_jac};
+                 &d->dbgH, &d->dbgb, &d->dbgdx, &d->dec_pts, &d->dec_codes, &d->dec_out, &d->dec_jac,
+                 &d->ray_nev, &d->ph_list, &d->ph_code};
   for (Buf* b : bufs)
     if (b->p) cudaFree(b->p);
   if (d->ev0) cudaEventDestroy(d->ev0);
@@ -394,7 +397,10 @@ static int launch_t3(qsp_decoder* d, bool jac, int grid, const float* pts, const
 
 static int launch_decoder(qsp_decoder* d, int mode, bool jac, const float* pts, const int* code_idx, const float* codes,
                           int code_stride, long n, const int* n_dev, int n_codes_y, float* sdf, float* jacp,
-                          cudaStream_t st) {
+                          cudaStream_t st, const int* row_map = nullptr) {
+  if (row_map && (jac || (mode != DEC_FAST && mode != DEC_FP32))) { g_err = "row_map: forward passes only"; return QSP_ERR_INVALID; }
+  TcDecoderDev tc = d->tc;
+  tc.row_map = row_map;
   const int rows_per_tile = mode == DEC_FAST ? 128 : 64;
   long tiles = n_dev ? (long)d->num_sms : ((n + rows_per_tile - 1) / rows_per_tile) * n_codes_y;
   if (tiles <= 0) return QSP_OK;
@@ -402,9 +408,9 @@ static int launch_decoder(qsp_decoder* d, int mode, bool jac, const float* pts, 
   if (mode != DEC_FP32) {
 #define TC_LAUNCH(M, J)                                                                                              \
   do {                                                                                                               \
-    int r_ = d->pair ? launch_clustered(k_decoder_tc<M, J, 2>, std::min<int>(grid.x, d->pair_grid), 2, TC_SMEM_BYTES, st, d->tc, pts, \
+    int r_ = d->pair ? launch_clustered(k_decoder_tc<M, J, 2>, std::min<int>(grid.x, d->pair_grid), 2, TC_SMEM_BYTES, st, tc, pts, \
                                         code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp)               \
-                     : launch_clustered(k_decoder_tc<M, J, 1>, grid.x, 1, TC_SMEM_BYTES, st, d->tc, pts, code_idx, codes, \
+                     : launch_clustered(k_decoder_tc<M, J, 1>, grid.x, 1, TC_SMEM_BYTES, st, tc, pts, code_idx, codes, \
                                         code_stride, n_codes_y, n, n_dev, sdf, jacp);                               \
     if (r_) return r_;                                                                                               \
   } while (0)
@@ -429,10 +435,12 @@ static int launch_decoder(qsp_decoder* d, int mode, bool jac, const float* pts, 
     CK(cudaGetLastError());
     return QSP_OK;
   }
+  DecoderDev dw = d->dw;
+  dw.row_map = row_map;
   if (jac)
-    k_decoder_ffma<true><<<grid, FF_THREADS, FF_SMEM_BYTES, st>>>(d->dw, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
+    k_decoder_ffma<true><<<grid, FF_THREADS, FF_SMEM_BYTES, st>>>(dw, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
   else
-    k_decoder_ffma<false><<<grid, FF_THREADS, FF_SMEM_BYTES, st>>>(d->dw, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
+    k_decoder_ffma<false><<<grid, FF_THREADS, FF_SMEM_BYTES, st>>>(dw, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
   LAUNCHED();
   CK(cudaGetLastError());
   return QSP_OK;
@@ -593,9 +601,12 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
 
   ObjState* state; int *counters, *ray_obj, *pt_obj, *ray_cnt, *ray_base, *band_cnt, *band_base;
   float *q_pts, *q_sdf, *slot, *ray_res, *jp_pts, *g_sdf, *g_jac, *row_fac, *row_res, *partials, *d_rec;
-  int *q_code, *q_samp, *cand_q, *jp_code, *row_ray, *row_samp;
+  int *q_code, *q_samp, *cand_q, *jp_code, *row_ray, *row_samp, *ray_nev, *ph_list, *ph_code;
   ENSURE(d->state, B, state);
-  ENSURE(d->counters, 8, counters);
+  ENSURE(d->counters, 8 + GN_MAXC, counters);
+  ENSURE(d->ray_nev, R, ray_nev);
+  ENSURE(d->ph_list, qcap, ph_list);
+  ENSURE(d->ph_code, qcap, ph_code);
   ENSURE(d->ray_obj, R, ray_obj);
   ENSURE(d->pt_obj, M, pt_obj);
   ENSURE(d->ray_cnt, R, ray_cnt);
@@ -645,20 +656,31 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
   const int first_mode = d->precision == QSP_PREC_FP32_CORES ? DEC_FP32 : DEC_FAST;
   const float cand_lim = p.th + (first_mode == DEC_FAST ? QSP_FAST_MARGIN : 0.f);
   const int cand_blocks = (int)((bandcap + tb - 1) / tb);
-  CK(cudaMemsetAsync(counters, 0, 8 * sizeof(int), st));
+  CK(cudaMemsetAsync(counters, 0, (8 + GN_MAXC) * sizeof(int), st));
+  int* phase_cnt = counters + 8;
+  const int n_phases = d->phases ? (S + 31) / 32 : 1;
   for (int it = 0; it < prm->num_iterations; ++it) {
-    k_prep<<<(B + 63) / 64, 64, 0, st>>>(state, B, S); LAUNCHED();
+    k_prep<<<(B + 63) / 64, 64, 0, st>>>(state, B, S, phase_cnt); LAUNCHED();
     // (b) sample, in-ball test, ordered compaction
     k_sample<false><<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, R, S, ray_cnt, nullptr, nullptr, nullptr, nullptr); LAUNCHED();
     k_exclusive_scan<<<1, 1024, 0, st>>>(ray_cnt, ray_base, R, counters + 0, 0, nullptr); LAUNCHED();
     k_sample<true><<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, R, S, nullptr, ray_base, q_pts, q_code, q_samp); LAUNCHED();
     // (a) forward decode of the in-ball samples (loss.py:77-78), first pass
-    if ((r = launch_decoder(d, first_mode, false, q_pts, q_code, codes_dev, code_stride, 0, counters + 0, 1, q_sdf, nullptr, st))) return r;
+    // in phases of 32 samples along the ray; a ray stops at its first certainly-opaque sample (k_phase_list)
+    if (d->phases) {
+      for (int ph = 0; ph < n_phases; ++ph) {
+        k_phase_list<<<ray_blocks, tb, 0, st>>>(ph, R, ray_base, q_sdf, cand_lim, q_code, ray_nev, ph_list, ph_code, phase_cnt); LAUNCHED();
+        if ((r = launch_decoder(d, first_mode, false, q_pts, ph_code, codes_dev, code_stride, 0, phase_cnt + ph, 1, q_sdf, nullptr, st, ph_list))) return r;
+      }
+    } else {
+      if ((r = launch_decoder(d, first_mode, false, q_pts, q_code, codes_dev, code_stride, 0, counters + 0, 1, q_sdf, nullptr, st))) return r;
+    }
+    const int* nev = d->phases ? ray_nev : ray_cnt;     // decoded samples per ray
     // candidates near the band, appended behind the surface points in the Jacobian row list
-    k_candidates<false><<<ray_blocks, tb, 0, st>>>(ray_base, R, q_sdf, cand_lim, band_cnt, nullptr, M, (int)bandcap, nullptr,
+    k_candidates<false><<<ray_blocks, tb, 0, st>>>(ray_base, nev, R, q_sdf, cand_lim, band_cnt, nullptr, M, (int)bandcap, nullptr,
                                                    nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr); LAUNCHED();
     k_exclusive_scan<<<1, 1024, 0, st>>>(band_cnt, band_base, R, counters + 1, M, counters + 2); LAUNCHED();
-    k_candidates<true><<<ray_blocks, tb, 0, st>>>(ray_base, R, q_sdf, cand_lim, nullptr, band_base, M, (int)bandcap, q_pts,
+    k_candidates<true><<<ray_blocks, tb, 0, st>>>(ray_base, nev, R, q_sdf, cand_lim, nullptr, band_base, M, (int)bandcap, q_pts,
                                                   q_code, q_samp, jp_pts, jp_code, row_ray, row_samp, cand_q, counters + 3); LAUNCHED();
     k_surface_xform<<<std::max(1, (M + tb - 1) / tb), tb, 0, st>>>(state, in.pts, pt_obj, M, jp_pts, jp_code); LAUNCHED();
     // (a) SDF + input Jacobian of surface points and candidates (loss.py:34,144), fp32-equivalent
@@ -666,7 +688,7 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
     k_refine_scatter<<<cand_blocks, tb, 0, st>>>(counters + 1, (int)bandcap, cand_q, g_sdf, M, q_sdf); LAUNCHED();
     // (b) occupancy, transmittance, rendered depth, band selection
     k_render<<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, d_rays_off, in.depth, d_depth_off, R, S, p.th,
-                                        ray_base, q_sdf, slot, ray_res, ray_cnt); LAUNCHED();
+                                        ray_base, q_sdf, nev, slot, ray_res, band_cnt); LAUNCHED();
     k_row_factors<<<cand_blocks, tb, 0, st>>>(counters + 1, (int)bandcap, M, S, row_ray, row_samp, slot, ray_res,
                                               row_fac, row_res); LAUNCHED();
     // (c) chain rule + normal equations, (d) solve + update

@@ -23,6 +23,7 @@ struct DecoderDev {
   const float* w8;                // [512]
   float b8;
   int kf[8];                      // padded K of the forward layers: 80 for lin0, 512 otherwise
+  const int* row_map;             // optional (forward only): row i reads pts[row_map[i]] and writes sdf[row_map[i]]
 };
 
 // Per-object Gauss-Newton state kept on the device between iterations (floats, 128 per object).

@@ -69,11 +69,12 @@ k_decoder_ffma(DecoderDev dw, const float* __restrict__ pts, const int* __restri
       long r = row0 + i;
       bool ok = r < n;
       const float* cz = (code_idx && ok) ? codes + (size_t)code_idx[r] * code_stride : out_code;
+      const long rp = (dw.row_map && ok) ? dw.row_map[r] : r;
       for (int c = lane; c < 80; c += 32) {
         float v = 0.f;
         if (ok) {
           if (c < QSP_CODE) v = cz[c];
-          else if (c < QSP_IN) v = pts[r * 3 + (c - QSP_CODE)];
+          else if (c < QSP_IN) v = pts[rp * 3 + (c - QSP_CODE)];
         }
         act[(warp * 8 + i) * QSP_HID + c] = v;
         if (c < QSP_JSTRIDE) inp[(warp * 8 + i) * QSP_JSTRIDE + c] = v;
@@ -174,7 +175,7 @@ k_decoder_ffma(DecoderDev dw, const float* __restrict__ pts, const int* __restri
             p = warp_sum(p);
             float sv = tanhf(p + dw.b8);
             srow[i] = sv;
-            if (lane == 0 && sdf_out && row0 + i < n) sdf_out[row0 + i] = sv;
+            if (lane == 0 && sdf_out && row0 + i < n) sdf_out[dw.row_map ? dw.row_map[row0 + i] : row0 + i] = sv;
           }
           if (JAC) {  // seed of the reverse sweep: d tanh * w8, masked by lin7's ReLU
             __syncwarp();

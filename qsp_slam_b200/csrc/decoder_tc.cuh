@@ -54,6 +54,8 @@ struct TcDecoderDev {
   const float* bias;                              // [8][512] fp32, zero padded
   const float* w8;                                // [512] fp32
   float b8;
+  const int* row_map;                             // optional (k_decoder_tc forward only): row i reads pts[row_map[i]] and
+                                                  // writes sdf[row_map[i]]; code_idx stays indexed by i
 };
 
 __device__ __forceinline__ uint32_t pack_h2(float a, float b) {
@@ -275,6 +277,7 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
       const long grow = tile * ROWS + pl;                // global row of this thread's point
       const bool valid = grow < n;
       const float* my_code = (code_idx && valid) ? codes + (size_t)code_idx[grow] * code_stride : pass_code;
+      const long prow = (!JAC && dw.row_map && valid) ? dw.row_map[grow] : grow;   // row of pts / sdf_out
       // ---- stage the input rows [code, xyz, 0...] into K-blocks 0,1 (loss_utils.py:71-72) ----
       // Group g owns K-blocks {g, g+2} of each accumulator half (two 32-column chunks each), so K-blocks 4h, 4h+1
       // are rewritten after half of a half's epilogue and 4h+2, 4h+3 at its end - the order the next layer's MMAs
@@ -298,7 +301,10 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
           } else {
 #pragma unroll
             for (int u = 0; u < 16; ++u) cv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (ok) cv[0] = make_float4(pts[r * 3], pts[r * 3 + 1], pts[r * 3 + 2], 0.f);
+            if (ok) {
+              const long rp = (!JAC && dw.row_map) ? dw.row_map[r] : r;
+              cv[0] = make_float4(pts[rp * 3], pts[rp * 3 + 1], pts[rp * 3 + 2], 0.f);
+            }
           }
 #pragma unroll
           for (int c8 = 0; c8 < 8; ++c8) {
@@ -410,7 +416,7 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
 #pragma unroll
                   for (int j = 0; j < CW; ++j) {
                     const int c = colb + j - QSP_SKIP_COL;
-                    if (c >= 0) f[j] = !valid ? 0.f : c < QSP_CODE ? my_code[c] : pts[grow * 3 + (c - QSP_CODE)];
+                    if (c >= 0) f[j] = !valid ? 0.f : c < QSP_CODE ? my_code[c] : pts[prow * 3 + (c - QSP_CODE)];
                   }
                 }
                 if (l == 7) {                                               // lin8: 512 -> 1
@@ -489,7 +495,7 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
             for (int u = 0; u < TC_NG; ++u) tot += part[u * 128 + pl];
             sdf_v = tanhf(tot);
           }
-          if (g == 0 && (MODE != TC_SPLIT || !odd) && valid && sdf_o) sdf_o[grow] = sdf_v;
+          if (g == 0 && (MODE != TC_SPLIT || !odd) && valid && sdf_o) sdf_o[prow] = sdf_v;
           if (JAC) {
             // seed of the reverse sweep: SG * (1 - s^2) * w8, masked by lin7's ReLU (loss_utils.py:100-101)
             const float d = (1.f - sdf_v * sdf_v) * TC_SG;

@@ -75,8 +75,9 @@ __global__ void k_init_state(ObjState* st, const float* __restrict__ t_cam_obj,
 
 // depth range, background depth and rotation prior of the current pose (optimizer.py:144-153,
 // loss.py:155-178)
-__global__ void k_prep(ObjState* st, int B, int S) {
+__global__ void k_prep(ObjState* st, int B, int S, int* phase_cnt) {
   int o = blockIdx.x * blockDim.x + threadIdx.x;
+  if (phase_cnt && o < GN_MAXC) phase_cnt[o] = 0;      // row counts of this iteration's first-pass phases
   if (o >= B) return;
   ObjState& s = st[o];
   if (s.failed) return;
@@ -159,6 +160,36 @@ __global__ void k_sample(const ObjState* __restrict__ st, const float* __restric
   if (!FILL && lane == 0) ray_cnt[r] = cnt;
 }
 
+// First pass in phases along the ray (front to back).  Phase p decodes in-ball samples [32p, 32p + 32) of every
+// ray that has not met a certainly-opaque sample (first-pass s <= -lim, hence exact s <= -th and occupancy exactly
+// 1, loss_utils.py:46-47) in an earlier phase: behind such a sample the transmittance cumprod(1 - o) is exactly 0
+// (loss.py:99), so those samples weigh 0 in the rendered depth (:106-114) and have de_do = 0 (:118-125) - their SDF
+// is never needed.  One warp per ray appends its rows to the phase's list (order within the list is irrelevant:
+// the decoder scatters through the list) and records how many of the ray's samples have been decoded.
+__global__ void k_phase_list(int p, int R, const int* __restrict__ ray_base, const float* __restrict__ q_sdf,
+                             float lim, const int* __restrict__ q_code, int* __restrict__ ray_nev,
+                             int* __restrict__ list, int* __restrict__ list_code, int* __restrict__ phase_cnt) {
+  int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (r >= R) return;
+  const int lo = ray_base[r], n = ray_base[r + 1] - lo, start = p * 32;
+  if (p == 0 && lane == 0) ray_nev[r] = 0;
+  if (start >= n) return;
+  if (p > 0) {
+    const int nev = ray_nev[r];
+    const float s = q_sdf[lo + start - 32 + lane];       // the previous phase's 32 samples of this ray
+    if (__any_sync(0xffffffffu, s <= -lim) || nev != start) return;
+  }
+  const int m = min(32, n - start);
+  int base = 0;
+  if (lane == 0) base = atomicAdd(phase_cnt + p, m);
+  base = __shfl_sync(0xffffffffu, base, 0);
+  if (lane < m) {
+    list[base + lane] = lo + start + lane;
+    list_code[base + lane] = q_code[lo + start + lane];
+  }
+  if (lane == 0) ray_nev[r] = start + m;
+}
+
 // exclusive scan of n ints into out[0..n] (out[n] = total); single block, fixed order
 __global__ void k_exclusive_scan(const int* __restrict__ in, int* __restrict__ out, int n,
                                  int* total, int total_add, int* total2) {
@@ -207,8 +238,8 @@ __global__ void k_render(ObjState* __restrict__ st, const float* __restrict__ ra
                          const int* __restrict__ ray_obj, const int* __restrict__ rays_off,
                          const float* __restrict__ depth, const int* __restrict__ depth_off,
                          int R, int S, float th, const int* __restrict__ ray_base,
-                         const float* __restrict__ q_sdf, float* __restrict__ slot_de_ds,
-                         float* __restrict__ ray_res, int* __restrict__ band_cnt) {
+                         const float* __restrict__ q_sdf, const int* __restrict__ ray_nev,
+                         float* __restrict__ slot_de_ds, float* __restrict__ ray_res, int* __restrict__ band_cnt) {
   int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (r >= R) return;
   int o = ray_obj[r];
@@ -221,6 +252,7 @@ __global__ void k_render(ObjState* __restrict__ st, const float* __restrict__ ra
   float occ[GN_MAXC], T[GN_MAXC], dj[GN_MAXC];
   bool band[GN_MAXC];
   int cnt = 0, base = ray_base[r];
+  const int nev = ray_nev[r];                          // samples behind it were not decoded: T is exactly 0 there
   const float inv2th = 2.f * th;
   // occupancy per sample; samples outside the ball keep occupancy 0 (loss.py:84-86)
 #pragma unroll
@@ -237,7 +269,8 @@ __global__ void k_render(ObjState* __restrict__ st, const float* __restrict__ ra
       }
       unsigned m = __ballot_sync(0xffffffffu, in);
       if (in) {
-        float s = q_sdf[base + cnt + __popc(m & ((1u << lane) - 1u))];
+        const int qi = cnt + __popc(m & ((1u << lane) - 1u));
+        float s = qi < nev ? q_sdf[base + qi] : -1.f;
         occ[ch] = __fsub_rn(0.5f, __fdiv_rn(fminf(fmaxf(s, -th), th), inv2th));  // loss_utils.py:46-47
         band[ch] = (s > -th) && (s < th);                                        // loss.py:88
       }
@@ -246,6 +279,7 @@ __global__ void k_render(ObjState* __restrict__ st, const float* __restrict__ ra
   }
   // transmittance T_j = prod_{l<=j} (1 - o_l)  (loss.py:99) and rendered depth (loss.py:100-114)
   float carry = 1.f, du = 0.f;
+  int nband = 0;                                       // band samples in front of the ray's first opaque sample
 #pragma unroll
   for (int ch = 0; ch < GN_MAXC; ++ch) {
     if (ch < nc) {
@@ -261,6 +295,7 @@ __global__ void k_render(ObjState* __restrict__ st, const float* __restrict__ ra
       int j = ch * 32 + lane;
       T[ch] = j < S ? incl : 0.f;
       du += (j < S) ? dj[ch] * (occ[ch] * prev) : 0.f;
+      nband += __popc(__ballot_sync(0xffffffffu, band[ch] && prev > 0.f));
       carry = __shfl_sync(0xffffffffu, incl, 31);
     }
   }
@@ -294,9 +329,6 @@ __global__ void k_render(ObjState* __restrict__ st, const float* __restrict__ ra
       kept += __popc(__ballot_sync(0xffffffffu, out != 0.f));
     }
   }
-  int nband = 0;
-#pragma unroll
-  for (int ch = 0; ch < GN_MAXC; ++ch) nband += __popc(__ballot_sync(0xffffffffu, band[ch]));
   if (lane == 0) {
     band_cnt[r] = kept;
     ray_res[r] = res;
@@ -691,7 +723,8 @@ __global__ void k_finalize_pose_only(const ObjState* __restrict__ st, const floa
 // Order: (ray, sample) ascending, i.e. the order torch.where gives (loss.py:68,89-90).
 // ------------------------------------------------------------------------------------------------
 template <bool FILL>
-__global__ void k_candidates(const int* __restrict__ ray_base, int R, const float* __restrict__ q_sdf,
+__global__ void k_candidates(const int* __restrict__ ray_base, const int* __restrict__ ray_nev, int R,
+                             const float* __restrict__ q_sdf,
                              float lim, int* __restrict__ cand_cnt, const int* __restrict__ cand_base,
                              int row0, int cap, const float* __restrict__ q_pts, const int* __restrict__ q_code,
                              const int* __restrict__ q_samp, float* __restrict__ jp_pts, int* __restrict__ jp_code,
@@ -699,7 +732,7 @@ __global__ void k_candidates(const int* __restrict__ ray_base, int R, const floa
                              int* __restrict__ overflow) {
   int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (r >= R) return;
-  const int lo = ray_base[r], hi = ray_base[r + 1];
+  const int lo = ray_base[r], hi = lo + ray_nev[r];     // the decoded samples of the ray (k_phase_list)
   int cnt = 0;
   const int base = FILL ? cand_base[r] : 0;
   for (int i0 = lo; i0 < hi; i0 += 32) {

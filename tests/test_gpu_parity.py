@@ -135,11 +135,13 @@ def test_one_gn_iteration_vs_reference_and_oracle(golden, dev, orc, name, style,
                        torch.from_numpy(golden[p + "rays"]), torch.from_numpy(golden[p + "depth"]))
     ren = o["render"]
     assert it["n_inball"] == ren["valid_ray"].shape[0]
-    # n_band is a diagnostic: band samples behind a ray's first opaque sample never get the exact SDF in the product
-    # path (they cannot be kept, k_candidates), so there it is counted on the first-pass value - it can differ from
-    # the reference count only by samples whose |s| is within the first-pass margin of th
-    near = int(((ren["sdf"].abs() - prm.th).abs() < 0.006).sum())
-    assert abs(it["n_band"] - ren["band_ray"].shape[0]) <= (0 if precision == "fp32" else near)
+    # n_band counts the band samples in front of the ray's first opaque sample (exact s <= -th): behind it the
+    # transmittance is exactly 0, such samples can never be kept and the product path does not decode them
+    vi, vj, sv = ren["valid_ray"].numpy(), ren["valid_sample"].numpy(), ren["sdf"].numpy()
+    first_opq = np.full(golden[p + "rays"].shape[0], 1 << 30)
+    np.minimum.at(first_opq, vi[sv <= -prm.th], vj[sv <= -prm.th])
+    bi, bj = ren["band_ray"].numpy(), ren["band_sample"].numpy()
+    assert it["n_band"] == int((bj < first_opq[bi]).sum())
     assert it["n_keep"] == ren["keep_ray"].shape[0]
     assert np.array_equal(it["keep_ray"], ren["keep_ray"].numpy())
     assert np.array_equal(it["keep_sample"], ren["keep_sample"].numpy())
@@ -363,3 +365,29 @@ def test_three_product_pair_kernel_vs_fp64_oracle(decoder_state, orc):
     for c in range(3):
         ref = G.decode_sdf(fd64, torch.from_numpy(codes[c]), torch.from_numpy(x)).numpy()
         assert np.abs(got[c] - ref).max() < 1e-5
+
+
+@pytest.mark.parametrize("name,style", [("kitti0", "kitti"), ("redwood1", "redwood")])
+def test_phased_first_pass_is_bit_identical_to_the_full_one(golden, decoder_state, name, style):
+    """Stopping a ray's first pass at its first certainly-opaque sample (k_phase_list) drops only samples of exactly
+    zero weight: the candidate rows, their order and therefore every sum of the iteration are the same as with all
+    in-ball samples decoded (QSP_PHASES=0).  Three iterations, so that a later iteration starts from identical
+    states too."""
+    p = name + "_"
+    outs = []
+    for ph in ("1", "0"):
+        d = _decoder_with_env(decoder_state, QSP_PHASES=ph)
+        opt = make_opt(d, style, 3)
+        opt.set_debug(True)
+        out = opt.reconstruct_object(golden[p + "t_cam_obj"], golden[p + "pts"], golden[p + "rays"],
+                                     golden[p + "depth"], golden[p + "code0"])
+        outs.append((out, [opt.get_iteration(i) for i in range(3)]))
+    (o1, it1), (o0, it0) = outs
+    assert o1.is_good and o0.is_good
+    np.testing.assert_array_equal(o1.t_cam_obj, o0.t_cam_obj)
+    np.testing.assert_array_equal(o1.code, o0.code)
+    for a, b in zip(it1, it0):
+        for k in ("n_inball", "n_band", "n_keep", "n_cand"):
+            assert a[k] == b[k]
+        for k in ("keep_ray", "keep_sample", "H", "b", "dx"):
+            np.testing.assert_array_equal(a[k], b[k])
