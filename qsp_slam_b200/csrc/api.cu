@@ -654,13 +654,14 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
 
   // first pass over the ray samples: single-pass fp16 tensor kernel + margin, or the exact kernel
   const int first_mode = d->precision == QSP_PREC_FP32_CORES ? DEC_FP32 : DEC_FAST;
-  const float cand_lim = p.th + (first_mode == DEC_FAST ? QSP_FAST_MARGIN : 0.f);
+  const float margin0 = first_mode == DEC_FAST ? QSP_FAST_MARGIN0 : 0.f;
+  const float margin1 = first_mode == DEC_FAST ? QSP_FAST_MARGIN_PER_NORM : 0.f;
   const int cand_blocks = (int)((bandcap + tb - 1) / tb);
   CK(cudaMemsetAsync(counters, 0, (8 + GN_MAXC) * sizeof(int), st));
   int* phase_cnt = counters + 8;
   const int n_phases = d->phases ? (S + 31) / 32 : 1;
   for (int it = 0; it < prm->num_iterations; ++it) {
-    k_prep<<<(B + 63) / 64, 64, 0, st>>>(state, B, S, phase_cnt); LAUNCHED();
+    k_prep<<<(B + 63) / 64, 64, 0, st>>>(state, B, S, phase_cnt, p.th, margin0, margin1); LAUNCHED();
     // (b) sample, in-ball test, ordered compaction
     k_sample<false><<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, R, S, ray_cnt, nullptr, nullptr, nullptr, nullptr); LAUNCHED();
     k_exclusive_scan<<<1, 1024, 0, st>>>(ray_cnt, ray_base, R, counters + 0, 0, nullptr); LAUNCHED();
@@ -669,7 +670,7 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
     // in phases of 32 samples along the ray; a ray stops at its first certainly-opaque sample (k_phase_list)
     if (d->phases) {
       for (int ph = 0; ph < n_phases; ++ph) {
-        k_phase_list<<<ray_blocks, tb, 0, st>>>(ph, R, ray_base, q_sdf, cand_lim, q_code, ray_nev, ph_list, ph_code, phase_cnt); LAUNCHED();
+        k_phase_list<<<ray_blocks, tb, 0, st>>>(ph, R, state, ray_obj, ray_base, q_sdf, q_code, ray_nev, ph_list, ph_code, phase_cnt); LAUNCHED();
         if ((r = launch_decoder(d, first_mode, false, q_pts, ph_code, codes_dev, code_stride, 0, phase_cnt + ph, 1, q_sdf, nullptr, st, ph_list))) return r;
       }
     } else {
@@ -677,10 +678,10 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
     }
     const int* nev = d->phases ? ray_nev : ray_cnt;     // decoded samples per ray
     // candidates near the band, appended behind the surface points in the Jacobian row list
-    k_candidates<false><<<ray_blocks, tb, 0, st>>>(ray_base, nev, R, q_sdf, cand_lim, band_cnt, nullptr, M, (int)bandcap, nullptr,
+    k_candidates<false><<<ray_blocks, tb, 0, st>>>(state, ray_obj, ray_base, nev, R, q_sdf, band_cnt, nullptr, M, (int)bandcap, nullptr,
                                                    nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr); LAUNCHED();
     k_exclusive_scan<<<1, 1024, 0, st>>>(band_cnt, band_base, R, counters + 1, M, counters + 2); LAUNCHED();
-    k_candidates<true><<<ray_blocks, tb, 0, st>>>(ray_base, nev, R, q_sdf, cand_lim, nullptr, band_base, M, (int)bandcap, q_pts,
+    k_candidates<true><<<ray_blocks, tb, 0, st>>>(state, ray_obj, ray_base, nev, R, q_sdf, nullptr, band_base, M, (int)bandcap, q_pts,
                                                   q_code, q_samp, jp_pts, jp_code, row_ray, row_samp, cand_q, counters + 3); LAUNCHED();
     k_surface_xform<<<std::max(1, (M + tb - 1) / tb), tb, 0, st>>>(state, in.pts, pt_obj, M, jp_pts, jp_code); LAUNCHED();
     // (a) SDF + input Jacobian of surface points and candidates (loss.py:34,144), fp32-equivalent

@@ -10,7 +10,11 @@
 #define QSP_JSTRIDE 68
 #define QSP_NDOF_ 71
 #define QSP_NTRI 2556             // 71*72/2 upper-triangle entries of J^T J
-#define QSP_FAST_MARGIN 0.006f    // candidate band = th + margin; the single-pass fp16 SDF error stays below ~2e-3
+// Candidate band of an object = th + margin, margin = QSP_FAST_MARGIN0 + QSP_FAST_MARGIN_PER_NORM * |code|: the error
+// of the single-pass fp16 first pass grows with the code norm (scripts/fast_error_tail.py, 72 M rows over three
+// decoders: max 2.9e-3 at |z| = 0, 4.2e-3 at |z| ~ 0.8, 8.1e-3 at |z| ~ 2.4); the margin stays >= 1.5x above it.
+#define QSP_FAST_MARGIN0 0.0045f
+#define QSP_FAST_MARGIN_PER_NORM 0.004f
 #define QSP_PART_STRIDE 2640      // 2556 (H) + 71 (b) + 1 (sum of robust residual^2) padded to a multiple of 16
 
 // Folded decoder weights on the device (fp32 copies for the exact FFMA path).
@@ -36,8 +40,9 @@ struct ObjState {
   float res_rot;
   float loss;                     // loss of the last completed iteration (optimizer.py:205)
   int failed;                     // set at the reference's early exits (optimizer.py:161-194)
-  int n_inball, n_band, n_keep;   // Q, band size, P of the current iteration
-  int pad[19];
+  int n_inball, n_band, n_keep;   // Q, visible band size, P of the current iteration
+  float cand_lim;                 // first-pass |s| below which a sample is re-evaluated exactly (th + margin)
+  int pad[18];
 };
 static_assert(sizeof(ObjState) == 128 * 4, "ObjState layout");
 

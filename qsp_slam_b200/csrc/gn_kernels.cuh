@@ -75,7 +75,7 @@ __global__ void k_init_state(ObjState* st, const float* __restrict__ t_cam_obj,
 
 // depth range, background depth and rotation prior of the current pose (optimizer.py:144-153,
 // loss.py:155-178)
-__global__ void k_prep(ObjState* st, int B, int S, int* phase_cnt) {
+__global__ void k_prep(ObjState* st, int B, int S, int* phase_cnt, float th, float margin0, float margin_per_norm) {
   int o = blockIdx.x * blockDim.x + threadIdx.x;
   if (phase_cnt && o < GN_MAXC) phase_cnt[o] = 0;      // row counts of this iteration's first-pass phases
   if (o >= B) return;
@@ -92,6 +92,9 @@ __global__ void k_prep(ObjState* st, int B, int S, int* phase_cnt) {
   s.d_max = __fadd_rn(s.T_co[11], scale);
   s.delta_d = __fdiv_rn(__fsub_rn(s.d_max, s.d_min), (float)(S - 1));
   s.n_inball = s.n_band = s.n_keep = 0;
+  float zz = 0.f;
+  for (int c = 0; c < QSP_CODE; ++c) zz = fmaf(s.code[c], s.code[c], zz);
+  s.cand_lim = th + margin0 + margin_per_norm * sqrtf(zz);
   // rotation prior: res = 1 - (R_co e_y).n_g = 1 + R_co[1][1]
   double rc[9], ro[9], dd;
   for (int r = 0; r < 3; ++r)
@@ -166,8 +169,9 @@ __global__ void k_sample(const ObjState* __restrict__ st, const float* __restric
 // (loss.py:99), so those samples weigh 0 in the rendered depth (:106-114) and have de_do = 0 (:118-125) - their SDF
 // is never needed.  One warp per ray appends its rows to the phase's list (order within the list is irrelevant:
 // the decoder scatters through the list) and records how many of the ray's samples have been decoded.
-__global__ void k_phase_list(int p, int R, const int* __restrict__ ray_base, const float* __restrict__ q_sdf,
-                             float lim, const int* __restrict__ q_code, int* __restrict__ ray_nev,
+__global__ void k_phase_list(int p, int R, const ObjState* __restrict__ st, const int* __restrict__ ray_obj,
+                             const int* __restrict__ ray_base, const float* __restrict__ q_sdf,
+                             const int* __restrict__ q_code, int* __restrict__ ray_nev,
                              int* __restrict__ list, int* __restrict__ list_code, int* __restrict__ phase_cnt) {
   int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (r >= R) return;
@@ -175,6 +179,7 @@ __global__ void k_phase_list(int p, int R, const int* __restrict__ ray_base, con
   if (p == 0 && lane == 0) ray_nev[r] = 0;
   if (start >= n) return;
   if (p > 0) {
+    const float lim = st[ray_obj[r]].cand_lim;
     const int nev = ray_nev[r];
     const float s = q_sdf[lo + start - 32 + lane];       // the previous phase's 32 samples of this ray
     if (__any_sync(0xffffffffu, s <= -lim) || nev != start) return;
@@ -715,17 +720,17 @@ __global__ void k_finalize_pose_only(const ObjState* __restrict__ st, const floa
 }
 
 // ------------------------------------------------------------------------------------------------
-// candidate rows: in-ball samples whose first-pass SDF lies within +-lim of zero (lim = th + margin
-// when the first pass is the single-pass fp16 kernel, lim = th when it is exact).  They are
+// candidate rows: in-ball samples whose first-pass SDF lies within +-lim of zero (lim = the object's
+// cand_lim: th + margin when the first pass is the single-pass fp16 kernel, th when it is exact).  They are
 // re-evaluated, with the input Jacobian, by the fp32-equivalent kernel; every true band point
 // (loss.py:88) that can pass the de_do test is among them as long as the first-pass error stays below the
 // margin; samples behind a ray's first certainly-opaque sample are left out (see below).
 // Order: (ray, sample) ascending, i.e. the order torch.where gives (loss.py:68,89-90).
 // ------------------------------------------------------------------------------------------------
 template <bool FILL>
-__global__ void k_candidates(const int* __restrict__ ray_base, const int* __restrict__ ray_nev, int R,
-                             const float* __restrict__ q_sdf,
-                             float lim, int* __restrict__ cand_cnt, const int* __restrict__ cand_base,
+__global__ void k_candidates(const ObjState* __restrict__ st, const int* __restrict__ ray_obj,
+                             const int* __restrict__ ray_base, const int* __restrict__ ray_nev, int R,
+                             const float* __restrict__ q_sdf, int* __restrict__ cand_cnt, const int* __restrict__ cand_base,
                              int row0, int cap, const float* __restrict__ q_pts, const int* __restrict__ q_code,
                              const int* __restrict__ q_samp, float* __restrict__ jp_pts, int* __restrict__ jp_code,
                              int* __restrict__ row_ray, int* __restrict__ row_samp, int* __restrict__ cand_q,
@@ -733,6 +738,7 @@ __global__ void k_candidates(const int* __restrict__ ray_base, const int* __rest
   int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (r >= R) return;
   const int lo = ray_base[r], hi = lo + ray_nev[r];     // the decoded samples of the ray (k_phase_list)
+  const float lim = st[ray_obj[r]].cand_lim;
   int cnt = 0;
   const int base = FILL ? cand_base[r] : 0;
   for (int i0 = lo; i0 < hi; i0 += 32) {

@@ -53,14 +53,19 @@ def test_decoder_sdf_and_jacobian_vs_reference(golden, dev, mode):
 
 
 def test_fast_fp16_pass_is_within_its_margin(golden, dev):
-    """The single-pass fp16 kernel only pre-classifies ray samples; its error must stay well inside
-    the candidate margin (QSP_FAST_MARGIN = 6e-3) so that no true band point is missed."""
+    """The single-pass fp16 kernel only pre-classifies ray samples; its error must stay inside the object's
+    candidate margin 0.0045 + 0.004 |code| (common.cuh; the error grows with the code norm) so that no true band
+    point is missed.  scripts/fast_error_tail.py looks at 72 M rows; here 60 k rows per code norm."""
     s = dev.decode_sdf(golden["dec_z"], golden["dec_x"], mode="fast")
     assert np.abs(s - golden["dec_sdf"]).max() < 3e-3
-    x = synth._ball_points(np.random.default_rng(11), 60000)
-    a = dev.decode_sdf(golden["dec_z"], x, mode="fast")
-    b = dev.decode_sdf(golden["dec_z"], x, mode="tensor")
-    assert np.abs(a - b).max() < 4e-3
+    rng = np.random.default_rng(11)
+    x = synth._ball_points(rng, 60000)
+    for sigma in (0.0, 0.1, 0.3, 0.6):
+        z = (rng.standard_normal(64) * sigma).astype(np.float32)
+        a = dev.decode_sdf(z, x, mode="fast")
+        b = dev.decode_sdf(z, x, mode="tensor")
+        margin = 0.0045 + 0.004 * float(np.linalg.norm(z))
+        assert np.abs(a - b).max() < 0.75 * margin, (sigma, np.abs(a - b).max(), margin)
 
 
 def test_decoder_vs_oracle_ragged_sizes(dev, orc):
