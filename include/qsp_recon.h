@@ -38,7 +38,8 @@ enum {
   QSP_FLAG_HOST_PTRS = 1,    /* data pointers are host memory; the call copies h2d/d2h itself */
   QSP_FLAG_SYNC = 2,         /* cudaStreamSynchronize before returning */
   QSP_FLAG_FAST_FP16 = 4,    /* qsp_decode_sdf only: single-pass fp16 operands (|err| ~ 3e-4), 3-4x faster */
-  QSP_FLAG_FP32_CORES = 8    /* decode calls: exact-fp32 CUDA-core kernel instead of the tensor-core one */
+  QSP_FLAG_FP32_CORES = 8,   /* decode calls: exact-fp32 CUDA-core kernel instead of the tensor-core one */
+  QSP_FLAG_EXACT_GRID = 16   /* qsp_extract_mesh only: fp32-equivalent SDF at every grid point (validation) */
 };
 
 /* Arithmetic of the decoder inside the GN loop.  TENSOR (default): tcgen05 tensor-core kernel with
@@ -133,6 +134,18 @@ int qsp_mesh_extract(const float* sdf, int32_t D, float level, float spacing, co
 int qsp_mesh_sizes(const qsp_mesh* m, int32_t* n_vertices, int32_t* n_faces);
 int qsp_mesh_copy(const qsp_mesh* m, float* vertices, int32_t* faces);   /* host pointers */
 void qsp_mesh_free(qsp_mesh* m);
+
+/* --- grid decode + isosurface in one call: replaces MeshExtractor.extract_mesh_from_code --------- */
+/* (reconstruct/optimizer.py:292-304).  qsp_set_voxel_grid copies the (D^3,3) grid points that        */
+/* reconstruct/utils.py:98-117 create_voxel_grid produces to the device once (MeshExtractor.__init__, */
+/* optimizer.py:284-290); qsp_extract_mesh decodes `code` (64 floats; host with QSP_FLAG_HOST_PTRS)   */
+/* over it and runs the isosurface kernels on the device grid.  The SDF is fp32-equivalent at every   */
+/* corner of every cell the level set can cross (first-pass fp16 elsewhere, where no kernel reads the */
+/* value), so the mesh is bit-identical to the one of the exact grid (QSP_FLAG_EXACT_GRID).           */
+/* sdf_out: optional device/host (per flag) buffer receiving that D^3 grid.                           */
+int qsp_set_voxel_grid(qsp_decoder* dec, const float* pts, int32_t D, uint32_t flags, void* stream);
+int qsp_extract_mesh(qsp_decoder* dec, const float* code, float level, float spacing,
+                     const float* origin, float* sdf_out, uint32_t flags, void* stream, qsp_mesh** out);
 
 /* --- bookkeeping --------------------------------------------------------------------------------- */
 const char* qsp_last_error(void);

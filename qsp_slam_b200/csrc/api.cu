@@ -53,6 +53,8 @@ struct qsp_decoder {
   Buf pts_off, rays_off, depth_off, ray_obj, pt_obj;
   Buf state, counters, ray_cnt, ray_base, band_cnt, band_base;
   Buf q_pts, q_code, q_samp, cand_q, q_sdf, slot, ray_res, ray_nev, ph_list, ph_code;
+  Buf grid_pts, grid_sdf, grid_need, grid_list, grid_cnt, grid_code;   // qsp_extract_mesh
+  int grid_D = 0;
   Buf jp_pts, jp_code, g_sdf, g_jac, row_fac, row_res, row_ray, row_samp, row_active, m_active;
   Buf partials, dbgH, dbgb, dbgdx;
   Buf dec_pts, dec_codes, dec_out, dec_jac;
@@ -68,6 +70,7 @@ struct qsp_decoder {
   int cluster = 2;                                 // CTAs per cluster sharing a multicast weight stream
   int t3_grid = 148;
   bool phases = true;                              // first pass front to back in phases of 32 samples per ray
+  bool timeline = false;                           // QSP_TIMELINE=1: CUDA-event time of every launch group of one GN iteration
 };
 
 template <typename T>
@@ -306,6 +309,7 @@ extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_
   CK(cudaFuncSetAttribute(k_decoder_ffma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FF_SMEM_BYTES));
   CK(cudaFuncSetAttribute(k_decoder_ffma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FF_SMEM_BYTES));
   if (const char* e = getenv("QSP_PHASES")) d->phases = atoi(e) != 0;
+  if (const char* e = getenv("QSP_TIMELINE")) d->timeline = atoi(e) != 0;
   if (const char* dbg_env = getenv("QSP_TC_DEBUG")) {
     int v = atoi(dbg_env);
     CK(cudaMemcpyToSymbol(g_tc_dbg, &v, sizeof(int)));
@@ -326,7 +330,8 @@ extern "C" void qsp_decoder_destroy(qsp_decoder* d) {
                  &d->slot, &d->ray_res, &d->jp_pts, &d->jp_code, &d->g_sdf, &d->g_jac, &d->row_fac,
                  &d->row_res, &d->row_ray, &d->row_samp, &d->row_active, &d->m_active, &d->partials,
                  &d->dbgH, &d->dbgb, &d->dbgdx, &d->dec_pts, &d->dec_codes, &d->dec_out, &d->dec_jac,
-                 &d->ray_nev, &d->ph_list, &d->ph_code};
+                 &d->ray_nev, &d->ph_list, &d->ph_code, &d->grid_pts, &d->grid_sdf, &d->grid_need, &d->grid_list,
+                 &d->grid_cnt, &d->grid_code};
   for (Buf* b : bufs)
     if (b->p) cudaFree(b->p);
   if (d->ev0) cudaEventDestroy(d->ev0);
@@ -398,7 +403,7 @@ static int launch_t3(qsp_decoder* d, bool jac, int grid, const float* pts, const
 static int launch_decoder(qsp_decoder* d, int mode, bool jac, const float* pts, const int* code_idx, const float* codes,
                           int code_stride, long n, const int* n_dev, int n_codes_y, float* sdf, float* jacp,
                           cudaStream_t st, const int* row_map = nullptr) {
-  if (row_map && (jac || (mode != DEC_FAST && mode != DEC_FP32))) { g_err = "row_map: forward passes only"; return QSP_ERR_INVALID; }
+  if (row_map && (jac || d->t3 || n_codes_y != 1)) { g_err = "row_map: single-code forward passes only"; return QSP_ERR_INVALID; }
   TcDecoderDev tc = d->tc;
   tc.row_map = row_map;
   const int rows_per_tile = mode == DEC_FAST ? 128 : 64;
@@ -417,9 +422,9 @@ static int launch_decoder(qsp_decoder* d, int mode, bool jac, const float* pts, 
     if (mode == DEC_FAST && !jac)
       TC_LAUNCH(TC_FAST, false);
     else if (d->p3 && d->pair) {
-      int r_ = jac ? launch_clustered(k_decoder_p3<true>, std::min<int>(grid.x, d->pair_grid), 2, TC_SMEM_BYTES, st, d->tc, pts, code_idx,
+      int r_ = jac ? launch_clustered(k_decoder_p3<true>, std::min<int>(grid.x, d->pair_grid), 2, TC_SMEM_BYTES, st, tc, pts, code_idx,
                                       codes, code_stride, n_codes_y, n, n_dev, sdf, jacp)
-                   : launch_clustered(k_decoder_p3<false>, std::min<int>(grid.x, d->pair_grid), 2, TC_SMEM_BYTES, st, d->tc, pts, code_idx,
+                   : launch_clustered(k_decoder_p3<false>, std::min<int>(grid.x, d->pair_grid), 2, TC_SMEM_BYTES, st, tc, pts, code_idx,
                                       codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
       if (r_) return r_;
     } else if (d->t3) {
@@ -660,18 +665,33 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
   CK(cudaMemsetAsync(counters, 0, (8 + GN_MAXC) * sizeof(int), st));
   int* phase_cnt = counters + 8;
   const int n_phases = d->phases ? (S + 31) / 32 : 1;
+  std::vector<std::pair<const char*, cudaEvent_t>> marks;   // diagnostic timeline of the last iteration
+#define MARK(name)                                                        \
+  do {                                                                    \
+    if (d->timeline && it == prm->num_iterations - 1) {                   \
+      cudaEvent_t mark_ev;                                                \
+      CK(cudaEventCreate(&mark_ev));                                      \
+      CK(cudaEventRecord(mark_ev, st));                                   \
+      marks.emplace_back(name, mark_ev);                                  \
+    }                                                                     \
+  } while (0)
   for (int it = 0; it < prm->num_iterations; ++it) {
+    MARK("start");
     k_prep<<<(B + 63) / 64, 64, 0, st>>>(state, B, S, phase_cnt, p.th, margin0, margin1); LAUNCHED();
+    MARK("k_prep");
     // (b) sample, in-ball test, ordered compaction
     k_sample<false><<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, R, S, ray_cnt, nullptr, nullptr, nullptr, nullptr); LAUNCHED();
     k_exclusive_scan<<<1, 1024, 0, st>>>(ray_cnt, ray_base, R, counters + 0, 0, nullptr); LAUNCHED();
     k_sample<true><<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, R, S, nullptr, ray_base, q_pts, q_code, q_samp); LAUNCHED();
+    MARK("k_sample x2 + scan");
     // (a) forward decode of the in-ball samples (loss.py:77-78), first pass
     // in phases of 32 samples along the ray; a ray stops at its first certainly-opaque sample (k_phase_list)
     if (d->phases) {
       for (int ph = 0; ph < n_phases; ++ph) {
         k_phase_list<<<ray_blocks, tb, 0, st>>>(ph, R, state, ray_obj, ray_base, q_sdf, q_code, ray_nev, ph_list, ph_code, phase_cnt); LAUNCHED();
+        MARK("k_phase_list");
         if ((r = launch_decoder(d, first_mode, false, q_pts, ph_code, codes_dev, code_stride, 0, phase_cnt + ph, 1, q_sdf, nullptr, st, ph_list))) return r;
+        MARK("first-pass decoder");
       }
     } else {
       if ((r = launch_decoder(d, first_mode, false, q_pts, q_code, codes_dev, code_stride, 0, counters + 0, 1, q_sdf, nullptr, st))) return r;
@@ -684,18 +704,23 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
     k_candidates<true><<<ray_blocks, tb, 0, st>>>(state, ray_obj, ray_base, nev, R, q_sdf, nullptr, band_base, M, (int)bandcap, q_pts,
                                                   q_code, q_samp, jp_pts, jp_code, row_ray, row_samp, cand_q, counters + 3); LAUNCHED();
     k_surface_xform<<<std::max(1, (M + tb - 1) / tb), tb, 0, st>>>(state, in.pts, pt_obj, M, jp_pts, jp_code); LAUNCHED();
+    MARK("k_candidates x2 + scan + k_surface_xform");
     // (a) SDF + input Jacobian of surface points and candidates (loss.py:34,144), fp32-equivalent
     if ((r = launch_decoder(d, hp_mode, true, jp_pts, jp_code, codes_dev, code_stride, 0, counters + 2, 1, g_sdf, g_jac, st))) return r;
+    MARK("fwd+Jacobian decoder");
     k_refine_scatter<<<cand_blocks, tb, 0, st>>>(counters + 1, (int)bandcap, cand_q, g_sdf, M, q_sdf); LAUNCHED();
     // (b) occupancy, transmittance, rendered depth, band selection
     k_render<<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, d_rays_off, in.depth, d_depth_off, R, S, p.th,
                                         ray_base, q_sdf, nev, slot, ray_res, band_cnt); LAUNCHED();
     k_row_factors<<<cand_blocks, tb, 0, st>>>(counters + 1, (int)bandcap, M, S, row_ray, row_samp, slot, ray_res,
                                               row_fac, row_res); LAUNCHED();
+    MARK("k_refine_scatter + k_render + k_row_factors");
     // (c) chain rule + normal equations, (d) solve + update
     k_accumulate<<<dim3(nchunk, B, 2), 256, 0, st>>>(state, d_pts_off, d_rays_off, band_base, M, jp_pts, g_sdf, g_jac,
                                                      row_fac, row_res, p.b2, p.b1, 0, nullptr, partials); LAUNCHED();
+    MARK("k_accumulate");
     k_solve<<<B, 256, 0, st>>>(state, d_pts_off, nchunk, partials, p, 0, nullptr, dbgH, dbgb, dbgdx); LAUNCHED();
+    MARK("k_solve");
     CK(cudaGetLastError());
     if (d->debug) {  // parity inspection: copy this iteration's normal equations and index lists out
       CK(cudaStreamSynchronize(st));
@@ -722,8 +747,21 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
       d->dbg.push_back(std::move(g));
     }
   }
+#undef MARK
   k_finalize<<<(B + 63) / 64, 64, 0, st>>>(state, B, d_rec); LAUNCHED();
   CK(cudaGetLastError());
+  if (!marks.empty()) {
+    CK(cudaStreamSynchronize(st));
+    float total = 0.f;
+    for (size_t i = 1; i < marks.size(); ++i) {
+      float ms = 0.f;
+      CK(cudaEventElapsedTime(&ms, marks[i - 1].second, marks[i].second));
+      fprintf(stderr, "qsp timeline: %-48s %8.1f us\n", marks[i].first, ms * 1e3f);
+      total += ms;
+    }
+    fprintf(stderr, "qsp timeline: %-48s %8.1f us\n", "iteration", total * 1e3f);
+    for (auto& m : marks) cudaEventDestroy(m.second);
+  }
   if (host) {
     CK(cudaMemcpyAsync(records, d_rec, (size_t)B * QSP_RECORD_LEN * 4, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
@@ -843,52 +881,148 @@ struct qsp_mesh {
   float* verts = nullptr;   // device (nv,3)
   int* faces = nullptr;     // device (nf,3)
   int nv = 0, nf = 0;
+  cudaStream_t stream = nullptr;   // the stream the buffers were allocated on (stream-ordered pool)
 };
+
+// stream-ordered allocations from the device's default pool, kept across calls (no cudaMalloc/cudaFree round trips)
+static int pool_ready(int device) {
+  static std::atomic<unsigned long long> done{0};
+  if (done.load() & (1ull << device)) return QSP_OK;
+  cudaMemPool_t pool;
+  CK(cudaDeviceGetDefaultMemPool(&pool, device));
+  unsigned long long keep = ~0ull;
+  CK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+  done.fetch_or(1ull << device);
+  return QSP_OK;
+}
+
+// exclusive scan of n ints (out has n + 1 entries), any n: segments of 1024, totals scanned by one block
+static int scan_ints(const int* in, int* out, long n, int* seg_tmp, cudaStream_t st) {
+  const int nseg = (int)((n + SCAN_SEG - 1) / SCAN_SEG);
+  k_scan_segments<<<nseg, SCAN_SEG, 0, st>>>(in, out, (int)n, seg_tmp); LAUNCHED();
+  k_exclusive_scan<<<1, 1024, 0, st>>>(seg_tmp, seg_tmp + nseg, nseg, nullptr, 0, nullptr); LAUNCHED();
+  k_scan_add<<<nseg, SCAN_SEG, 0, st>>>(out, (int)n, seg_tmp + nseg, nseg); LAUNCHED();
+  return QSP_OK;
+}
+
+static int mesh_from_device_grid(const float* src, int32_t D, float level, float spacing, const float* origin,
+                                 cudaStream_t st, qsp_mesh** out) {
+  int dev = 0;
+  CK(cudaGetDevice(&dev));
+  int r = pool_ready(dev);
+  if (r) return r;
+  const size_t V = (size_t)D * D * D, Cn = (size_t)(D - 1) * (D - 1) * (D - 1);
+  const size_t nseg = (V + SCAN_SEG - 1) / SCAN_SEG;
+  unsigned char* vmask = nullptr;
+  int *vcount = nullptr, *vbase = nullptr, *tcount = nullptr, *tbase = nullptr, *seg = nullptr;
+  qsp_mesh* m = new qsp_mesh();
+  auto cleanup = [&]() {
+    cudaFreeAsync(vmask, st); cudaFreeAsync(vcount, st); cudaFreeAsync(vbase, st); cudaFreeAsync(tcount, st);
+    cudaFreeAsync(tbase, st); cudaFreeAsync(seg, st);
+  };
+#define CKM(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { g_err = std::string(#call) + ": " + cudaGetErrorString(e_); cleanup(); cudaFreeAsync(m->verts, st); cudaFreeAsync(m->faces, st); delete m; return QSP_ERR_CUDA; } } while (0)
+  CKM(cudaMallocAsync(&vmask, V, st));
+  CKM(cudaMallocAsync(&vcount, V * 4, st));
+  CKM(cudaMallocAsync(&vbase, (V + 1) * 4, st));
+  CKM(cudaMallocAsync(&tcount, Cn * 4, st));
+  CKM(cudaMallocAsync(&tbase, (Cn + 1) * 4, st));
+  CKM(cudaMallocAsync(&seg, (2 * nseg + 2) * 4, st));
+  const int tb = 256;
+  k_mt_vertex_flags<<<(unsigned)((V + tb - 1) / tb), tb, 0, st>>>(src, D, level, vmask, vcount); LAUNCHED();
+  scan_ints(vcount, vbase, (long)V, seg, st);
+  k_mt_cells<false><<<(unsigned)((Cn + tb - 1) / tb), tb, 0, st>>>(src, D, level, vmask, vbase, tcount, nullptr, nullptr); LAUNCHED();
+  scan_ints(tcount, tbase, (long)Cn, seg, st);
+  CKM(cudaMemcpyAsync(&m->nv, vbase + V, 4, cudaMemcpyDeviceToHost, st));
+  CKM(cudaMemcpyAsync(&m->nf, tbase + Cn, 4, cudaMemcpyDeviceToHost, st));
+  CKM(cudaStreamSynchronize(st));
+  CKM(cudaMallocAsync(&m->verts, (size_t)std::max(m->nv, 1) * 12, st));
+  CKM(cudaMallocAsync(&m->faces, (size_t)std::max(m->nf, 1) * 12, st));
+  k_mt_vertices<<<(unsigned)((V + tb - 1) / tb), tb, 0, st>>>(src, D, level, spacing, origin[0], origin[1], origin[2],
+                                                              vmask, vbase, m->verts); LAUNCHED();
+  k_mt_cells<true><<<(unsigned)((Cn + tb - 1) / tb), tb, 0, st>>>(src, D, level, vmask, vbase, nullptr, tbase, m->faces); LAUNCHED();
+  CKM(cudaGetLastError());
+  cleanup();
+  CKM(cudaStreamSynchronize(st));
+#undef CKM
+  m->stream = st;
+  *out = m;
+  return QSP_OK;
+}
 
 extern "C" int qsp_mesh_extract(const float* sdf, int32_t D, float level, float spacing, const float* origin,
                                 uint32_t flags, void* stream, qsp_mesh** out) {
   if (!sdf || !origin || !out || D < 2 || D > 1024) { g_err = "bad argument"; return QSP_ERR_INVALID; }
   cudaStream_t st = (cudaStream_t)stream;
-  const size_t V = (size_t)D * D * D, Cn = (size_t)(D - 1) * (D - 1) * (D - 1);
+  if (!(flags & QSP_FLAG_HOST_PTRS)) return mesh_from_device_grid(sdf, D, level, spacing, origin, st, out);
+  int dev = 0;
+  CK(cudaGetDevice(&dev));
+  int r = pool_ready(dev);
+  if (r) return r;
+  const size_t V = (size_t)D * D * D;
   float* dsdf = nullptr;
-  unsigned char* vmask = nullptr;
-  int *vcount = nullptr, *vbase = nullptr, *tcount = nullptr, *tbase = nullptr;
-  qsp_mesh* m = new qsp_mesh();
-  auto cleanup = [&]() {
-    if (flags & QSP_FLAG_HOST_PTRS) cudaFree(dsdf);
-    cudaFree(vmask); cudaFree(vcount); cudaFree(vbase); cudaFree(tcount); cudaFree(tbase);
-  };
-#define CKM(call) do { cudaError_t e_ = (call); if (e_ != cudaSuccess) { g_err = std::string(#call) + ": " + cudaGetErrorString(e_); cleanup(); cudaFree(m->verts); cudaFree(m->faces); delete m; return QSP_ERR_CUDA; } } while (0)
-  const float* src = sdf;
-  if (flags & QSP_FLAG_HOST_PTRS) {
-    CKM(cudaMalloc(&dsdf, V * 4));
-    CKM(cudaMemcpyAsync(dsdf, sdf, V * 4, cudaMemcpyHostToDevice, st));
-    src = dsdf;
-  }
-  CKM(cudaMalloc(&vmask, V));
-  CKM(cudaMalloc(&vcount, V * 4));
-  CKM(cudaMalloc(&vbase, (V + 1) * 4));
-  CKM(cudaMalloc(&tcount, Cn * 4));
-  CKM(cudaMalloc(&tbase, (Cn + 1) * 4));
-  const int tb = 256;
-  k_mt_vertex_flags<<<(unsigned)((V + tb - 1) / tb), tb, 0, st>>>(src, D, level, vmask, vcount); LAUNCHED();
-  k_exclusive_scan<<<1, 1024, 0, st>>>(vcount, vbase, (int)V, nullptr, 0, nullptr); LAUNCHED();
-  k_mt_cells<false><<<(unsigned)((Cn + tb - 1) / tb), tb, 0, st>>>(src, D, level, vmask, vbase, tcount, nullptr, nullptr); LAUNCHED();
-  k_exclusive_scan<<<1, 1024, 0, st>>>(tcount, tbase, (int)Cn, nullptr, 0, nullptr); LAUNCHED();
-  CKM(cudaMemcpyAsync(&m->nv, vbase + V, 4, cudaMemcpyDeviceToHost, st));
-  CKM(cudaMemcpyAsync(&m->nf, tbase + Cn, 4, cudaMemcpyDeviceToHost, st));
-  CKM(cudaStreamSynchronize(st));
-  CKM(cudaMalloc(&m->verts, (size_t)std::max(m->nv, 1) * 12));
-  CKM(cudaMalloc(&m->faces, (size_t)std::max(m->nf, 1) * 12));
-  k_mt_vertices<<<(unsigned)((V + tb - 1) / tb), tb, 0, st>>>(src, D, level, spacing, origin[0], origin[1], origin[2],
-                                                              vmask, vbase, m->verts); LAUNCHED();
-  k_mt_cells<true><<<(unsigned)((Cn + tb - 1) / tb), tb, 0, st>>>(src, D, level, vmask, vbase, nullptr, tbase, m->faces); LAUNCHED();
-  CKM(cudaGetLastError());
-  CKM(cudaStreamSynchronize(st));
-#undef CKM
-  cleanup();
-  *out = m;
+  CK(cudaMallocAsync(&dsdf, V * 4, st));
+  cudaError_t e = cudaMemcpyAsync(dsdf, sdf, V * 4, cudaMemcpyHostToDevice, st);
+  if (e != cudaSuccess) { g_err = std::string("cudaMemcpyAsync: ") + cudaGetErrorString(e); cudaFreeAsync(dsdf, st); return QSP_ERR_CUDA; }
+  r = mesh_from_device_grid(dsdf, D, level, spacing, origin, st, out);
+  cudaFreeAsync(dsdf, st);
+  return r;
+}
+
+extern "C" int qsp_set_voxel_grid(qsp_decoder* d, const float* pts, int32_t D, uint32_t flags, void* stream) {
+  if (!d || !pts || D < 2 || D > 1024) { g_err = "bad argument"; return QSP_ERR_INVALID; }
+  CK(cudaSetDevice(d->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const size_t V = (size_t)D * D * D;
+  float* g;
+  ENSURE(d->grid_pts, V * 3, g);
+  CK(cudaMemcpyAsync(g, pts, V * 12, (flags & QSP_FLAG_HOST_PTRS) ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, st));
+  CK(cudaStreamSynchronize(st));
+  d->grid_D = D;
   return QSP_OK;
+}
+
+extern "C" int qsp_extract_mesh(qsp_decoder* d, const float* code, float level, float spacing, const float* origin,
+                                float* sdf_out, uint32_t flags, void* stream, qsp_mesh** out) {
+  if (!d || !code || !origin || !out) { g_err = "bad argument"; return QSP_ERR_INVALID; }
+  if (d->grid_D < 2) { g_err = "qsp_set_voxel_grid has not been called"; return QSP_ERR_INVALID; }
+  CK(cudaSetDevice(d->device));
+  cudaStream_t st = (cudaStream_t)stream;
+  const int D = d->grid_D;
+  const size_t V = (size_t)D * D * D, Cn = (size_t)(D - 1) * (D - 1) * (D - 1);
+  const float* pts = reinterpret_cast<const float*>(d->grid_pts.p);
+  float *sdf, *dcode; unsigned char* need; int *list, *cnt;
+  ENSURE(d->grid_sdf, V, sdf);
+  ENSURE(d->grid_code, 64, dcode);
+  ENSURE(d->grid_need, V, need);
+  ENSURE(d->grid_list, V, list);
+  ENSURE(d->grid_cnt, 1, cnt);
+  CK(cudaMemcpyAsync(dcode, code, 64 * 4, (flags & QSP_FLAG_HOST_PTRS) ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, st));
+  int r;
+  const bool exact_cores = (flags & QSP_FLAG_FP32_CORES) || d->precision == QSP_PREC_FP32_CORES;
+  if (exact_cores || (flags & QSP_FLAG_EXACT_GRID)) {
+    if ((r = launch_decoder(d, exact_cores ? DEC_FP32 : DEC_SPLIT, false, pts, nullptr, dcode, 64, (long)V, nullptr, 1, sdf, nullptr, st))) return r;
+  } else {
+    float zz = 0.f;
+    if (flags & QSP_FLAG_HOST_PTRS) {
+      for (int c = 0; c < 64; ++c) zz += code[c] * code[c];
+    } else {
+      float hc[64];
+      CK(cudaMemcpyAsync(hc, dcode, sizeof(hc), cudaMemcpyDeviceToHost, st));
+      CK(cudaStreamSynchronize(st));
+      for (int c = 0; c < 64; ++c) zz += hc[c] * hc[c];
+    }
+    const float margin = QSP_FAST_MARGIN0 + QSP_FAST_MARGIN_PER_NORM * std::sqrt(zz);
+    const int tb = 256;
+    if ((r = launch_decoder(d, DEC_FAST, false, pts, nullptr, dcode, 64, (long)V, nullptr, 1, sdf, nullptr, st))) return r;
+    CK(cudaMemsetAsync(need, 0, V, st));
+    CK(cudaMemsetAsync(cnt, 0, 4, st));
+    k_grid_mark<<<(unsigned)((Cn + tb - 1) / tb), tb, 0, st>>>(sdf, D, level, margin, need); LAUNCHED();
+    k_grid_list<<<(unsigned)((V + tb - 1) / tb), tb, 0, st>>>(need, (long)V, list, cnt); LAUNCHED();
+    if ((r = launch_decoder(d, DEC_SPLIT, false, pts, nullptr, dcode, 64, 0, cnt, 1, sdf, nullptr, st, list))) return r;
+  }
+  if (sdf_out)
+    CK(cudaMemcpyAsync(sdf_out, sdf, V * 4, (flags & QSP_FLAG_HOST_PTRS) ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, st));
+  return mesh_from_device_grid(sdf, D, level, spacing, origin, st, out);
 }
 
 extern "C" int qsp_mesh_sizes(const qsp_mesh* m, int32_t* n_vertices, int32_t* n_faces) {
@@ -907,7 +1041,7 @@ extern "C" int qsp_mesh_copy(const qsp_mesh* m, float* vertices, int32_t* faces)
 
 extern "C" void qsp_mesh_free(qsp_mesh* m) {
   if (!m) return;
-  cudaFree(m->verts);
-  cudaFree(m->faces);
+  cudaFreeAsync(m->verts, m->stream);
+  cudaFreeAsync(m->faces, m->stream);
   delete m;
 }

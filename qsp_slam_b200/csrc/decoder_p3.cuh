@@ -189,6 +189,7 @@ k_decoder_p3(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
       const long grow = tile * P3_PTS + ptl;             // global row of this thread's point
       const bool valid = grow < n;
       const float* my_code = (code_idx && valid) ? codes + (size_t)code_idx[grow] * code_stride : pass_code;
+      const long prow = (!JAC && dw.row_map && valid) ? dw.row_map[grow] : grow;   // row of pts / sdf_out (forward only)
 
       // ---- stage the input rows [code, xyz, 0...] (loss_utils.py:71-72): the owners of K-block 0 write the code,
       //      the owners of K-block 1 xyz and the zero padding; all loads of a thread are in flight together ----
@@ -205,7 +206,7 @@ k_decoder_p3(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
           } else {
 #pragma unroll
             for (int u = 0; u < 16; ++u) cv[u] = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (valid) cv[0] = make_float4(pts[grow * 3], pts[grow * 3 + 1], pts[grow * 3 + 2], 0.f);
+            if (valid) cv[0] = make_float4(pts[prow * 3], pts[prow * 3 + 1], pts[prow * 3 + 2], 0.f);
           }
 #pragma unroll
           for (int cc = 0; cc < 2; ++cc) {
@@ -276,7 +277,7 @@ k_decoder_p3(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
 #pragma unroll
                   for (int j = 0; j < 32; ++j) {
                     const int c = feat0 + j - QSP_SKIP_COL;
-                    if (c >= 0) f[j] = !valid ? 0.f : c < QSP_CODE ? my_code[c] : pts[grow * 3 + (c - QSP_CODE)];
+                    if (c >= 0) f[j] = !valid ? 0.f : c < QSP_CODE ? my_code[c] : pts[prow * 3 + (c - QSP_CODE)];
                   }
                 }
                 if (l == 7) {                                                 // lin8: 512 -> 1
@@ -332,7 +333,7 @@ k_decoder_p3(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
           part[kbo * 64 + ptl] = psum;
           asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI) : "memory");
           sdf_v = tanhf(dw.b8 + ((part[ptl] + part[64 + ptl]) + (part[128 + ptl] + part[192 + ptl])));
-          if (kbo == 0 && valid && sdf_o) sdf_o[grow] = sdf_v;
+          if (kbo == 0 && valid && sdf_o) sdf_o[prow] = sdf_v;
           if (JAC) {
             // seed of the reverse sweep: SG * (1 - s^2) * w8, masked by lin7's ReLU (loss_utils.py:100-101)
             const float d = (1.f - sdf_v * sdf_v) * TC_SG;

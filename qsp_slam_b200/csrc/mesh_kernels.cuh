@@ -137,3 +137,84 @@ __global__ void k_mt_cells(const float* __restrict__ sdf, int D, float level,
   }
   if (!WRITE) tcount[c] = n;
 }
+
+// ------------------------------------------------------------------------------------------------
+// exclusive scan of n ints over many blocks (the grids have millions of entries): block-local scan of
+// 1024-entry segments + segment totals, scan of the totals (k_exclusive_scan, one block), add back.
+// out[0..n] with out[n] = total; deterministic.
+// ------------------------------------------------------------------------------------------------
+#define SCAN_SEG 1024
+__global__ void __launch_bounds__(SCAN_SEG) k_scan_segments(const int* __restrict__ in, int* __restrict__ out, int n,
+                                                            int* __restrict__ seg_sum) {
+  __shared__ int wsum[32];
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const long i = (long)blockIdx.x * SCAN_SEG + tid;
+  const int v = i < n ? in[i] : 0;
+  int x = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    int y = __shfl_up_sync(0xffffffffu, x, d);
+    if (lane >= d) x += y;
+  }
+  if (lane == 31) wsum[w] = x;
+  __syncthreads();
+  if (w == 0) {
+    int s = wsum[lane], t = s;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      int y = __shfl_up_sync(0xffffffffu, t, d);
+      if (lane >= d) t += y;
+    }
+    wsum[lane] = t - s;
+    if (lane == 31) seg_sum[blockIdx.x] = t;
+  }
+  __syncthreads();
+  if (i < n) out[i] = wsum[w] + x - v;
+}
+
+__global__ void __launch_bounds__(SCAN_SEG) k_scan_add(int* __restrict__ out, int n, const int* __restrict__ seg_base,
+                                                       int nseg) {
+  const long i = (long)blockIdx.x * SCAN_SEG + threadIdx.x;
+  if (i < n) out[i] += seg_base[blockIdx.x];
+  if (i == 0) out[n] = seg_base[nseg];
+}
+
+// ------------------------------------------------------------------------------------------------
+// Grid decode for the isosurface: only grid points that are corners of a cell the level set may cross need the
+// fp32-equivalent SDF - the isosurface kernels interpolate on edges with a sign change and never look at the
+// values of other cells.  A cell is ACTIVE when min(corner) - level < margin and max(corner) - level > -margin on
+// the first-pass values (|first pass - exact| < margin): every edge with a sign change, in the first-pass or in
+// the exact values, lies in active cells only, so the mesh of the mixed grid equals the mesh of the exact grid.
+// ------------------------------------------------------------------------------------------------
+__global__ void k_grid_mark(const float* __restrict__ sdf, int D, float level, float margin,
+                            unsigned char* __restrict__ need) {
+  const long c = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int E = D - 1;
+  if (c >= (long)E * E * E) return;
+  const int z = (int)(c % E), y = (int)((c / E) % E), x = (int)(c / ((long)E * E));
+  const long b = ((long)x * D + y) * D + z;
+  float lo = 1e30f, hi = -1e30f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) {
+    const float v = sdf[b + ((k >> 2) & 1) * (long)D * D + ((k >> 1) & 1) * D + (k & 1)] - level;
+    lo = fminf(lo, v); hi = fmaxf(hi, v);
+  }
+  if (lo < margin && hi > -margin) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) need[b + ((k >> 2) & 1) * (long)D * D + ((k >> 1) & 1) * D + (k & 1)] = 1;
+  }
+}
+
+// row list of the marked grid points (order irrelevant: the decoder gathers and scatters through it)
+__global__ void k_grid_list(const unsigned char* __restrict__ need, long V, int* __restrict__ list,
+                            int* __restrict__ count) {
+  const long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool f = i < V && need[i];
+  const unsigned m = __ballot_sync(0xffffffffu, f);
+  if (!m) return;
+  const int lane = threadIdx.x & 31;
+  int base = 0;
+  if (lane == __ffs(m) - 1) base = atomicAdd(count, __popc(m));
+  base = __shfl_sync(0xffffffffu, base, __ffs(m) - 1);
+  if (f) list[base + __popc(m & ((1u << lane) - 1u))] = (int)i;
+}

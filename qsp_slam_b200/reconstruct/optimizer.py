@@ -209,6 +209,16 @@ class MeshExtractor(object):
         self.code_len = code_len
         self.voxels_dim = voxels_dim
         self.voxel_points = create_voxel_grid(vol_dim=self.voxels_dim)
+        self._grid_on_device = False
+
+    def _ensure_device_grid(self):
+        """The grid points live on the device with the decoder handle (one handle may serve extractors of
+        different voxels_dim: the last one set wins, so it is re-sent when another extractor replaced it)."""
+        tag = (id(self), self.voxels_dim)
+        if getattr(self.decoder, "_voxel_grid_tag", None) != tag:
+            pts = np.ascontiguousarray(N.f32(self.voxel_points)[:, :3])
+            N.check(N.lib().qsp_set_voxel_grid(self.decoder.handle, N.ptr(pts), self.voxels_dim, N.FLAG_HOST_PTRS, None))
+            self.decoder._voxel_grid_tag = tag
 
     def decode_grid(self, codes) -> np.ndarray:
         """SDF over the voxel grid for one code (64,) -> (D,D,D) or several (C,64) -> (C,D,D,D)
@@ -221,9 +231,22 @@ class MeshExtractor(object):
         sdf = sdf.reshape(-1, D, D, D)
         return sdf[0] if single else sdf
 
-    def extract_mesh_from_code(self, code):
+    def extract_mesh_from_code(self, code, exact_grid: bool = False):
         """optimizer.py:292-304: grid decode, then marching cubes at level 0 with spacing 2/(D-1) and
-        origin (-1,-1,-1) (utils.py:120-141).  vertices (V,3) float32, faces (F,3) int32."""
+        origin (-1,-1,-1) (utils.py:120-141).  vertices (V,3) float32, faces (F,3) int32.
+        One native call (qsp_extract_mesh): the grid never leaves the device, and only the grid points whose value
+        the isosurface depends on get the fp32-equivalent evaluation - the mesh is bit-identical to the one of the
+        exact grid (``exact_grid=True``, the validation path)."""
+        from ..mesh import extract_mesh
+        self._ensure_device_grid()
+        voxel_size = 2.0 / (self.voxels_dim - 1)
+        code = N.f32(code).reshape(-1)[:self.code_len]
+        vertices, faces = extract_mesh(self.decoder.handle, code, 0.0, voxel_size, (-1.0, -1.0, -1.0), exact_grid)
+        return ForceKeyErrorDict(vertices=vertices, faces=faces)
+
+    def extract_mesh_from_code_reference_grid(self, code):
+        """The unfused form of the reference: ``decode_grid`` (fp32-equivalent everywhere, grid returned to the
+        host) followed by the isosurface kernels on that host grid.  Kept for the tests."""
         from ..mesh import marching_cubes
         sdf = self.decode_grid(code)
         voxel_size = 2.0 / (self.voxels_dim - 1)
@@ -231,13 +254,7 @@ class MeshExtractor(object):
         return ForceKeyErrorDict(vertices=vertices.astype("float32"), faces=faces.astype("int32"))
 
     def extract_meshes_from_codes(self, codes):
-        """Batch form used by the offline driver (extract_map_objects.py:44-61): the grids of all codes (C,64) are
-        decoded by one kernel launch (BASELINE config 4), then each goes through the isosurface kernels."""
-        from ..mesh import marching_cubes
-        sdf = self.decode_grid(np.asarray(codes, np.float32).reshape(-1, np.asarray(codes).shape[-1]))
-        voxel_size = 2.0 / (self.voxels_dim - 1)
-        out = []
-        for g in sdf:
-            vertices, faces = marching_cubes(g, 0.0, voxel_size, (-1.0, -1.0, -1.0))
-            out.append(ForceKeyErrorDict(vertices=vertices.astype("float32"), faces=faces.astype("int32")))
-        return out
+        """Batch form used by the offline driver (extract_map_objects.py:44-61): one native call per code, all on the
+        device; nothing but the meshes comes back."""
+        codes = np.asarray(codes, np.float32)
+        return [self.extract_mesh_from_code(c) for c in codes.reshape(-1, codes.shape[-1])]

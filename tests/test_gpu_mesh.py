@@ -82,3 +82,57 @@ def test_extract_mesh_from_code(decoder_state):
     # empty result for a level outside the value range
     v0, f0 = marching_cubes(sdf, 5.0, 2.0 / 31)
     assert v0.shape == (0, 3) and f0.shape == (0, 3)
+
+
+@pytest.mark.parametrize("D", [32, 64, 97])
+def test_fused_extraction_is_bit_identical_to_the_exact_grid(decoder_state, D):
+    """qsp_extract_mesh decodes only the corners of cells the level set can cross with the fp32-equivalent kernel
+    (first-pass fp16 elsewhere).  The isosurface kernels read nothing else, so vertices and faces must equal, bit for
+    bit, those of the exact grid - through the same call (QSP_FLAG_EXACT_GRID) and through the unfused
+    decode_grid + marching_cubes path of the reference (optimizer.py:292-304).  Codes of growing norm: the
+    first-pass error and with it the margin grow."""
+    from qsp_slam_b200.decoder import DeviceDecoder
+    from qsp_slam_b200.reconstruct.optimizer import MeshExtractor
+    from qsp_slam_b200.mesh import extract_mesh
+    dev = DeviceDecoder(decoder_state, 0)
+    mx = MeshExtractor(dev, 64, D)
+    rng = np.random.default_rng(D)
+    for sigma in (0.0, 0.1, 0.4):
+        code = (rng.standard_normal(64) * sigma).astype(np.float32)
+        m = mx.extract_mesh_from_code(code)
+        me = mx.extract_mesh_from_code(code, exact_grid=True)
+        mr = mx.extract_mesh_from_code_reference_grid(code)
+        if sigma <= 0.1:
+            assert m.vertices.shape[0] > 50              # (a large random code may have no zero level in the cube)
+        for other in (me, mr):
+            np.testing.assert_array_equal(m.vertices, other.vertices)
+            np.testing.assert_array_equal(m.faces, other.faces)
+        # the mixed grid: exact wherever it differs from the first pass, and exact on every crossing cell
+        v, f, g = extract_mesh(dev.handle, code, 0.0, 2.0 / (D - 1), return_grid_dim=D)
+        exact = mx.decode_grid(code)
+        fast = dev.decode_sdf(code, np.ascontiguousarray(np.asarray(mx.voxel_points)[:, :3]), mode="fast").reshape(D, D, D)
+        refined = g != fast
+        assert np.array_equal(g[refined], exact[refined])
+        assert refined.sum() < 0.5 * g.size and (refined.sum() > 0 or m.vertices.shape[0] == 0)
+        lo = np.minimum.reduce([exact[a:D - 1 + a, b:D - 1 + b, c:D - 1 + c] for a in (0, 1) for b in (0, 1) for c in (0, 1)])
+        hi = np.maximum.reduce([exact[a:D - 1 + a, b:D - 1 + b, c:D - 1 + c] for a in (0, 1) for b in (0, 1) for c in (0, 1)])
+        cross = (lo < 0) & (hi >= 0)
+        for a in (0, 1):
+            for b in (0, 1):
+                for c in (0, 1):
+                    sub_g = g[a:D - 1 + a, b:D - 1 + b, c:D - 1 + c]
+                    sub_e = exact[a:D - 1 + a, b:D - 1 + b, c:D - 1 + c]
+                    assert np.array_equal(sub_g[cross], sub_e[cross])
+
+
+def test_two_extractors_share_one_decoder(decoder_state):
+    """One decoder handle, extractors of different voxels_dim (LocalMapping.cc:45,65 builds one per class): each call
+    re-sends its grid when the other extractor replaced it."""
+    from qsp_slam_b200.decoder import DeviceDecoder
+    from qsp_slam_b200.reconstruct.optimizer import MeshExtractor
+    dev = DeviceDecoder(decoder_state, 0)
+    a, b = MeshExtractor(dev, 64, 24), MeshExtractor(dev, 64, 40)
+    z = np.zeros(64, np.float32)
+    ma, mb, ma2 = a.extract_mesh_from_code(z), b.extract_mesh_from_code(z), a.extract_mesh_from_code(z)
+    assert np.array_equal(ma.vertices, ma2.vertices) and np.array_equal(ma.faces, ma2.faces)
+    assert mb.vertices.shape[0] > ma.vertices.shape[0]
