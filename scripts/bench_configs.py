@@ -49,4 +49,14 @@ for mode in ("tensor", "fast"):
     ms = dev.last_kernel_ms(); n = 64 * grid.shape[0]
     out.append(dict(config="mesh_grid_128cubed_x64", mode=mode, seconds=ms / 1e3, evals_per_s=n / (ms / 1e3),
                     tflops_algorithmic=n * 3.67104e6 / (ms * 1e-3) / 1e12))
+# the whole of MeshExtractor.extract_mesh_from_code (host code in, host vertices/faces out), 64 codes
+from qsp_slam_b200.reconstruct.optimizer import MeshExtractor
+for D in (64, 128):
+    mx = MeshExtractor(dev, 64, D)
+    cz = codes.cpu().numpy()
+    mx.extract_mesh_from_code(cz[0])
+    tm = timed(lambda: [mx.extract_mesh_from_code(c) for c in cz])
+    nv = sum(mx.extract_mesh_from_code(c).vertices.shape[0] for c in cz[:4]) / 4
+    out.append(dict(config="mesh_extract_%dcubed_x64" % D, seconds=tm, meshes_per_s=64 / tm, ms_per_mesh=tm / 64 * 1e3,
+                    mean_vertices=nv, api="MeshExtractor.extract_mesh_from_code (host code in, host mesh out)"))
 for o in out: print(json.dumps(o))
