@@ -536,6 +536,18 @@ __device__ inline void exp_sim3_dev(const float* x, float* M, bool se3) {
   M[15] = 1.f;
 }
 
+// 1/sqrt(a) in fp64 on the critical path of every Cholesky column: fp32 rsqrt seed + two Newton steps (relative
+// error 2e-7 -> 9e-14 -> below fp64 rounding) instead of the long-latency sqrt and divide sequences
+__device__ __forceinline__ double rsqrt_f64(double a) {
+  const float af = (float)a;
+  if (!(af > 1e-30f && af < 1e30f)) return 1.0 / sqrt(a);
+  double y = (double)rsqrtf(af);
+  const double h = 0.5 * a;
+  y = y * (1.5 - h * y * y);
+  y = y * (1.5 - h * y * y);
+  return y;
+}
+
 // ------------------------------------------------------------------------------------------------
 // kernel (d): per-object reduction of the partial sums, assembly of the damped normal equations
 // (optimizer.py:205,218-252), Cholesky solve (the reference inverts H with LAPACK on the CPU, :254;
@@ -556,27 +568,52 @@ k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
   const int M = m_active ? m_active[o] : pts_off[o + 1] - pts_off[o], P = s.n_keep, Q = s.n_inball;
   const int n = pose_only ? 6 : 71;
   const float ws = pose_only ? 1.f : p.k2, wr = pose_only ? 0.f : p.k1;
-  // fixed-order reduction of the chunk partials; entry e of the 72x72 upper triangle
-  for (int e = tid; e < 2628; e += blockDim.x) {
-    float ss = 0.f, sr = 0.f;                           // fixed-order sums over the chunks, loads 8 at a time
-    const float* ps = partials + ((size_t)o * 2 + 0) * nchunk * QSP_PART_STRIDE + e;
-    const float* pr = partials + ((size_t)o * 2 + 1) * nchunk * QSP_PART_STRIDE + e;
-    for (int c0 = 0; c0 < nchunk; c0 += 8) {
-      float vs[8], vr[8];
+  // fixed-order reduction of the chunk partials; entry e of the 72x72 upper triangle.  A thread owns entries
+  // tid + 256 k; the loads of 6 entries x 4 chunks x 2 terms are in flight together, the sums run over the chunks
+  // in ascending order
+  {
+    constexpr int NE = 2628, EPT = (NE + 255) / 256;
+    float ss[EPT], sr[EPT];
 #pragma unroll
-      for (int c = 0; c < 8; ++c) {
-        vs[c] = c0 + c < nchunk ? ps[(size_t)(c0 + c) * QSP_PART_STRIDE] : 0.f;
-        vr[c] = (c0 + c < nchunk && !pose_only) ? pr[(size_t)(c0 + c) * QSP_PART_STRIDE] : 0.f;
+    for (int k = 0; k < EPT; ++k) ss[k] = sr[k] = 0.f;
+    const float* ps0 = partials + ((size_t)o * 2 + 0) * nchunk * QSP_PART_STRIDE;
+    const float* pr0 = partials + ((size_t)o * 2 + 1) * nchunk * QSP_PART_STRIDE;
+    for (int c0 = 0; c0 < nchunk; c0 += 4) {
+#pragma unroll
+      for (int half = 0; half < 2; ++half) {
+        float vs[6][4], vr[6][4];
+#pragma unroll
+        for (int kk = 0; kk < 6; ++kk) {
+          const int k = half * 6 + kk, e = tid + k * 256;
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const bool ok = k < EPT && e < NE && c0 + c < nchunk;
+            vs[kk][c] = ok ? ps0[(size_t)(c0 + c) * QSP_PART_STRIDE + e] : 0.f;
+            vr[kk][c] = (ok && !pose_only) ? pr0[(size_t)(c0 + c) * QSP_PART_STRIDE + e] : 0.f;
+          }
+        }
+#pragma unroll
+        for (int kk = 0; kk < 6; ++kk) {
+          const int k = half * 6 + kk;
+          if (k < EPT) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) { ss[k] += vs[kk][c]; sr[k] += vr[kk][c]; }
+          }
+        }
       }
-#pragma unroll
-      for (int c = 0; c < 8; ++c) { ss += vs[c]; sr += vr[c]; }
     }
-    int i = 0, r = e;
-    while (r >= 72 - i) { r -= 72 - i; ++i; }
-    int j = i + r;
-    float v = pose_only ? ss / (float)M : wr * sr / (float)P + ws * ss / (float)M;
-    A[i][j] = (double)v;                                // fp32 values, held exactly
-    A[j][i] = (double)v;
+#pragma unroll
+    for (int k = 0; k < EPT; ++k) {
+      const int e = tid + k * 256;
+      if (e < NE) {
+        int i = 0, r = e;
+        while (r >= 72 - i) { r -= 72 - i; ++i; }
+        const int j = i + r;
+        const float v = pose_only ? ss[k] / (float)M : wr * sr[k] / (float)P + ws * ss[k] / (float)M;
+        A[i][j] = (double)v;                              // fp32 values, held exactly
+        A[j][i] = (double)v;
+      }
+    }
   }
   __syncthreads();
   if (tid == 0) {
@@ -614,37 +651,81 @@ k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
   }
   if (dbg_b && tid < n) dbg_b[o * 71 + tid] = (float)rhs[tid];
   __syncthreads();
-  // In-place Cholesky A = L L^T (lower), fp64, with the right-hand side carried as row n of the lower
-  // triangle (forward substitution comes for free).  One barrier per column: column k is left UNSCALED in
-  // memory (nothing touches it after step k), every thread applies 1/sqrt(A[k][k]) on the fly, and
-  // rhs[k] keeps that factor, so L_ik = A[i][k] * rhs[k] and y_k = A[n][k] * rhs[k].
+  // Cholesky A = L L^T (lower), fp64, with the right-hand side carried as row n of the lower triangle (forward
+  // substitution comes for free).  One barrier per column: column k is left UNSCALED in shared memory (nothing
+  // touches it after step k), every thread applies 1/sqrt(A[k][k]) on the fly, and rhs[k] keeps that factor, so
+  // L_ik = A[i][k] * rhs[k] and y_k = A[n][k] * rhs[k].
   if (tid < n) A[n][tid] = rhs[tid];
   __syncthreads();
   {
-    const int ti = tid >> 4, tj = tid & 15;               // 16 x 16 threads over the trailing block
-    for (int k = 0; k < n; ++k) {
-      const double inv = 1.0 / sqrt(A[k][k]);
-      if (tid == 0) rhs[k] = inv;
-      const double inv2 = inv * inv;
-      for (int i = k + 1 + ti; i <= n; i += 16) {
-        const double aik = A[i][k] * inv2;
-        const int jmax = i < n ? i : n - 1;
-        for (int j = k + 1 + tj; j <= jmax; j += 16) A[i][j] -= aik * A[j][k];
+    // Thread (ti, tj) of a 16 x 16 arrangement keeps its elements A[ti + 16a][tj + 16b], b <= a, of the working
+    // matrix in registers; smem holds the finished (unscaled) columns.  Step k: the owners of column k publish it
+    // to smem, one barrier, every thread reads its column entries and updates its registers.  Entries that are not
+    // part of the lower triangle, or lie in finished rows / columns, see a zero factor: no predicates in the
+    // update.  Columns are walked in blocks of 16 (bk) so that every register index is static.
+    const int ti = tid >> 4, tj = tid & 15;
+    double R[5][5];
+#pragma unroll
+    for (int a = 0; a < 5; ++a)
+#pragma unroll
+      for (int b = 0; b <= a; ++b) {
+        const int i = ti + 16 * a, j = tj + 16 * b;
+        R[a][b] = (i <= n && j < n && j <= i) ? A[i][j] : 0.0;
       }
-      __syncthreads();
+#pragma unroll
+    for (int bk = 0; bk < 5; ++bk) {
+      const int kend = min(n, 16 * bk + 16);
+      for (int k = 16 * bk; k < kend; ++k) {
+        if (tj == (k & 15)) {
+#pragma unroll
+          for (int a = bk; a < 5; ++a) {
+            const int i = ti + 16 * a;
+            if (i >= k && i <= n) A[i][k] = R[a][bk];
+          }
+        }
+        __syncthreads();
+        const double inv = rsqrt_f64(A[k][k]);
+        if (tid == 0) rhs[k] = inv;
+        const double inv2 = inv * inv;
+        double ci[5], cj[5];
+#pragma unroll
+        for (int a = bk; a < 5; ++a) {
+          const int i = ti + 16 * a, j = tj + 16 * a;
+          ci[a] = (i > k && i <= n) ? A[i][k] * inv2 : 0.0;
+          cj[a] = (j > k && j < n) ? A[j][k] : 0.0;
+        }
+#pragma unroll
+        for (int a = bk; a < 5; ++a)
+#pragma unroll
+          for (int b = bk; b <= a; ++b) R[a][b] -= ci[a] * cj[b];
+      }
     }
+    __syncthreads();
   }
-  // back substitution L^T x = y by one warp, column oriented: x_i = y_i / L_ii, then y_j -= L_ij x_i (j < i)
+  // back substitution L^T x = y by one warp, column oriented, y in registers (lane owns entries lane, lane + 32,
+  // lane + 64): x_i = y_i / L_ii, then y_j -= L_ij x_i for j < i, with L_ij = A[i][j] * rhs[j], L_ii = 1 / rhs[i]
   if (tid < 32) {
-    for (int j = tid; j < n; j += 32) A[n][j] *= rhs[j];             // y
-    __syncwarp();
-    for (int i = n - 1; i >= 0; --i) {
-      const double xi = A[n][i] * rhs[i];                            // L_ii = 1 / rhs[i]
-      __syncwarp();
-      for (int j = tid; j < i; j += 32) A[n][j] -= (A[i][j] * rhs[j]) * xi;
-      if (tid == 0) A[n][i] = xi;
-      __syncwarp();
+    double y[3], rj[3];
+#pragma unroll
+    for (int u = 0; u < 3; ++u) {
+      const int j = tid + 32 * u;
+      rj[u] = j < n ? rhs[j] : 0.0;
+      y[u] = j < n ? A[n][j] * rj[u] : 0.0;
     }
+    for (int i = n - 1; i >= 0; --i) {
+      const int own = i >> 5;
+      const double yi = own == 0 ? y[0] : own == 1 ? y[1] : y[2];
+      const double xi = __shfl_sync(0xffffffffu, yi, i & 31) * rhs[i];
+#pragma unroll
+      for (int u = 0; u < 3; ++u) {
+        const int j = tid + 32 * u;
+        if (j < i) y[u] -= (A[i][j] * rj[u]) * xi;
+        else if (j == i) y[u] = xi;
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 3; ++u)
+      if (tid + 32 * u < n) A[n][tid + 32 * u] = y[u];
   }
   __syncthreads();
   if (tid < n) rhs[tid] = A[n][tid];
