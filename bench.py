@@ -225,7 +225,7 @@ def main():
         opt.reconstruct_objects(objs)
         its = [opt.get_iteration(5, b) for b in range(B)]
         opt.set_debug(False)
-        q_rows = sum(i["n_inball"] for i in its)
+        q_rows = sum(i["n_first_pass"] for i in its)   # ray samples the first pass decodes (of n_inball in the ball)
         j_rows = sum(o["pts"].shape[0] for o in objs) + sum(i["n_cand"] for i in its)
         g = torch.Generator(device="cuda").manual_seed(1)
         def ball(n):
@@ -285,7 +285,9 @@ def main():
                "clocks": clocks, "gpu_launches": int(launches),
                "e2e": {"value": e2e, "unit": "objects/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
                "roofline": roof, "cpu_baseline": cpu,
-               "decoder_evals_per_s": {k: v["rows"] / (v["ms"] * 1e-3) for k, v in kern.items()}}
+               "decoder_evals_per_s": {k: v["rows"] / (v["ms"] * 1e-3) for k, v in kern.items()},
+               "rows_per_iteration": {"in_ball_samples": sum(i["n_inball"] for i in its), "first_pass": q_rows,
+                                      "fwd_jac": j_rows, "kept_band": sum(i["n_keep"] for i in its)}}
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()

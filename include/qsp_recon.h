@@ -112,8 +112,9 @@ int qsp_estimate_pose_batch(qsp_decoder* dec, int32_t num_iterations, int32_t B,
                             float* out, uint32_t flags, void* stream);
 
 /* --- inspection of the last qsp_reconstruct_batch call (parity tests) -------------------------- */
-/* Per-iteration normal equations of object b: H (71,71), bvec (71), dx (71), counts (4) =
- * {in-ball samples Q, band points, kept band points P, failed flag}.  Host pointers.  Only
+/* Per-iteration normal equations of object b: H (71,71), bvec (71), dx (71), counts (6) =
+ * {in-ball samples Q, band points in front of the ray's first opaque sample, kept band points P,
+ * failed flag, ray samples the first pass decoded, candidate rows re-evaluated exactly}.  Host pointers.  Only
  * recorded when the handle is in debug mode (qsp_set_debug(dec,1)), which syncs per iteration. */
 int qsp_set_debug(qsp_decoder* dec, int32_t on);
 int qsp_get_iteration(qsp_decoder* dec, int32_t iteration, int32_t b, float* H, float* bvec,

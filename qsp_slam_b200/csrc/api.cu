@@ -36,7 +36,7 @@ struct Buf {
 
 struct IterDebug {
   std::vector<float> H, b, dx;         // (B,71,71), (B,71), (B,71)
-  std::vector<int> counts;             // (B,4)
+  std::vector<int> counts;             // (B,6)
   std::vector<int> band_off, row_ray, row_samp;   // candidate rows (ray-major)
   std::vector<float> row_fac;                     // de_ds of the row; 0 = not a kept band point
 };
@@ -726,7 +726,9 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
       CK(cudaStreamSynchronize(st));
       IterDebug g;
       g.H.resize((size_t)B * 71 * 71); g.b.resize((size_t)B * 71); g.dx.resize((size_t)B * 71);
-      g.counts.resize((size_t)B * 4); g.band_off.resize(R + 1);
+      g.counts.resize((size_t)B * 6); g.band_off.resize(R + 1);
+      std::vector<int> h_nev(std::max(R, 1));
+      CK(cudaMemcpy(h_nev.data(), nev, (size_t)R * 4, cudaMemcpyDeviceToHost));
       CK(cudaMemcpy(g.H.data(), dbgH, g.H.size() * 4, cudaMemcpyDeviceToHost));
       CK(cudaMemcpy(g.b.data(), dbgb, g.b.size() * 4, cudaMemcpyDeviceToHost));
       CK(cudaMemcpy(g.dx.data(), dbgdx, g.dx.size() * 4, cudaMemcpyDeviceToHost));
@@ -734,8 +736,12 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
       std::vector<ObjState> hs(B);
       CK(cudaMemcpy(hs.data(), state, (size_t)B * sizeof(ObjState), cudaMemcpyDeviceToHost));
       for (int o = 0; o < B; ++o) {
-        g.counts[o * 4 + 0] = hs[o].n_inball; g.counts[o * 4 + 1] = hs[o].n_band;
-        g.counts[o * 4 + 2] = hs[o].n_keep; g.counts[o * 4 + 3] = hs[o].failed;
+        g.counts[o * 6 + 0] = hs[o].n_inball; g.counts[o * 6 + 1] = hs[o].n_band;
+        g.counts[o * 6 + 2] = hs[o].n_keep; g.counts[o * 6 + 3] = hs[o].failed;
+        int fp = 0;
+        for (int rr = rays_off[o]; rr < rays_off[o + 1]; ++rr) fp += h_nev[rr];
+        g.counts[o * 6 + 4] = hs[o].failed ? 0 : fp;
+        g.counts[o * 6 + 5] = std::min<int>(g.band_off[rays_off[o + 1]], (int)bandcap) - std::min<int>(g.band_off[rays_off[o]], (int)bandcap);
       }
       int P = std::min<int>(g.band_off[R], (int)bandcap);
       g.row_ray.resize(P); g.row_samp.resize(P); g.row_fac.resize(P);
@@ -784,7 +790,7 @@ extern "C" int qsp_get_iteration(qsp_decoder* d, int32_t it, int32_t b, float* H
   if (H) memcpy(H, g.H.data() + (size_t)b * 71 * 71, 71 * 71 * 4);
   if (bvec) memcpy(bvec, g.b.data() + (size_t)b * 71, 71 * 4);
   if (dx) memcpy(dx, g.dx.data() + (size_t)b * 71, 71 * 4);
-  if (counts) memcpy(counts, g.counts.data() + (size_t)b * 4, 4 * 4);
+  if (counts) memcpy(counts, g.counts.data() + (size_t)b * 6, 6 * 4);
   return QSP_OK;
 }
 

@@ -192,14 +192,15 @@ class Optimizer(object):
         H = np.empty((71, 71), np.float32)
         bv = np.empty(71, np.float32)
         dx = np.empty(71, np.float32)
-        cnt = np.empty(4, np.int32)
+        cnt = np.empty(6, np.int32)
         N.check(N.lib().qsp_get_iteration(self.decoder.handle, iteration, b, N.ptr(H), N.ptr(bv), N.ptr(dx), N.ptr(cnt)))
         ray = np.empty(max(int(cnt[2]), 1), np.int32)
         smp = np.empty(max(int(cnt[2]), 1), np.int32)
         n = N.check(N.lib().qsp_get_band_indices(self.decoder.handle, iteration, b, N.ptr(ray), N.ptr(smp), ray.size))
         n_cand = N.check(N.lib().qsp_get_band_indices(self.decoder.handle, iteration, b, None, None, -1))
         return dict(H=H, b=bv, dx=dx, n_inball=int(cnt[0]), n_band=int(cnt[1]), n_keep=int(cnt[2]),
-                    failed=bool(cnt[3]), keep_ray=ray[:n], keep_sample=smp[:n], n_cand=n_cand)
+                    failed=bool(cnt[3]), keep_ray=ray[:n], keep_sample=smp[:n], n_cand=n_cand,
+                    n_first_pass=int(cnt[4]))
 
 
 class MeshExtractor(object):
