@@ -95,7 +95,7 @@ def cpu_port_objects_per_s(state, cfg, objs, threads=None):
     return len(objs) / dt, dt, torch.get_num_threads()
 
 
-def run_reference(args, rank):
+def run_reference(args, rank, real_stdout):
     """CPU arm: the oracle port with all host threads, each step a bounded sample of the workload."""
     if rank != 0:
         return
@@ -124,7 +124,7 @@ def run_reference(args, rank):
         "cpu_baseline": {"value": v, "unit": "objects/s", "cores": torch.get_num_threads(), "kind": "port",
                          "sample": sample},
         "e2e": {"value": v, "unit": "objects/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0}))
+        "gpu_launches": 0}), file=real_stdout, flush=True)
 
 
 def main():
@@ -139,8 +139,9 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    real_stdout = _json_only_stdout()
     if args.impl == "reference":
-        run_reference(args, rank)
+        run_reference(args, rank, real_stdout)
         return
 
     import torch
@@ -269,7 +270,7 @@ def main():
                              "note": "fp16 MMA flops issued by the kernel (fp32-equivalent arithmetic = 3 fp16 products)"},
                 "kernels": kern}
         cpu = None
-        if not args.no_cpu_baseline:
+        if not args.no_cpu_baseline and world == 1:      # rank 0 at N=1 only (torchrun pins OMP_NUM_THREADS=1)
             ns = min(B, 32)
             v, dt, th = cpu_port_objects_per_s(state, cfg, objs[:ns])
             cpu = {"value": v, "unit": "objects/s", "cores": th, "kind": "port",
@@ -292,7 +293,16 @@ def main():
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
-        print(json.dumps(out))
+        print(json.dumps(out), file=real_stdout, flush=True)
+
+
+def _json_only_stdout():
+    """Everything libraries write to file descriptor 1 (NCCL prints its version banner there) goes to stderr; the
+    returned file is the real stdout, used for the one JSON line."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    return real
 
 
 if __name__ == "__main__":
