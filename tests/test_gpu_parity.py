@@ -396,3 +396,36 @@ def test_phased_first_pass_is_bit_identical_to_the_full_one(golden, decoder_stat
             assert a[k] == b[k]
         for k in ("keep_ray", "keep_sample", "H", "b", "dx"):
             np.testing.assert_array_equal(a[k], b[k])
+
+
+@pytest.mark.parametrize("samples", [2, 31, 33, 64, 256])
+def test_depth_sample_counts_across_phase_boundaries(golden, dev, orc, samples):
+    """num_depth_samples from the minimum to the maximum the library takes (1..8 first-pass phases of 32 samples,
+    including counts that end right after a phase boundary): one GN iteration against the oracle - identical
+    in-ball / kept index sets, H, b, dx within the tensor-mode tolerances.  Too few in-ball samples must fail the way
+    the reference does (loss.py:73-74)."""
+    G, fd = orc
+    p = "kitti0_"
+    opt = make_opt(dev, "kitti", 1, samples=samples)
+    opt.set_debug(True)
+    try:
+        out = opt.reconstruct_object(golden[p + "t_cam_obj"], golden[p + "pts"], golden[p + "rays"],
+                                     golden[p + "depth"], golden[p + "code0"])
+        it = opt.get_iteration(0) if out.is_good else None
+    finally:
+        opt.set_debug(False)
+    prm = G.Params(synth.optimizer_config("kitti", num_depth_samples=samples, num_iterations=1))
+    t_oc = torch.inverse(torch.from_numpy(golden[p + "t_cam_obj"]))
+    o = G.gn_iteration(fd, prm, t_oc, torch.from_numpy(golden[p + "code0"]), torch.from_numpy(golden[p + "pts"]),
+                       torch.from_numpy(golden[p + "rays"]), torch.from_numpy(golden[p + "depth"]))
+    assert out.is_good == bool(o["ok"])
+    if not out.is_good:
+        return
+    ren = o["render"]
+    assert it["n_inball"] == ren["valid_ray"].shape[0]
+    assert it["n_first_pass"] <= it["n_inball"]
+    assert np.array_equal(it["keep_ray"], ren["keep_ray"].numpy())
+    assert np.array_equal(it["keep_sample"], ren["keep_sample"].numpy())
+    assert np.abs(it["H"] - o["H"].numpy()).max() < 5e-4 * np.abs(o["H"].numpy()).max()
+    assert np.abs(it["b"] - o["b"].numpy()).max() < 1e-3 * np.abs(o["b"].numpy()).max()
+    assert np.abs(it["dx"] - o["dx"].numpy()).max() < 3e-3 * np.abs(o["dx"].numpy()).max()
