@@ -61,3 +61,21 @@ def get_decoder(configs):
     """reconstruct/utils.py:get_decoder - the decoder named by ``configs.DeepSDF_DIR``."""
     from ..deep_sdf.workspace import config_decoder
     return config_decoder(configs.DeepSDF_DIR)
+
+
+def convert_sdf_voxels_to_mesh(sdf_3d):
+    """reconstruct/utils.py:120-141: level-0 isosurface of an (n,n,n) SDF grid (numpy array or torch tensor, host or
+    device) with spacing 2/(n-1) and origin (-1,-1,-1).  Returns (vertices (V,3) float32, faces (F,3) int32).  Runs on
+    the GPU (qsp_mesh_extract): marching tetrahedra, not scikit-image's Lewiner tables - same level set, different
+    triangulation."""
+    from ..mesh import marching_cubes
+    if hasattr(sdf_3d, "detach") and not sdf_3d.is_cuda:
+        sdf_3d = sdf_3d.detach().numpy()
+    n = int(sdf_3d.shape[0])
+    return marching_cubes(sdf_3d, 0.0, 2.0 / (n - 1), (-1.0, -1.0, -1.0))
+
+
+def write_mesh_to_ply(v, f, ply_filename_out):
+    """reconstruct/utils.py:144-164 (binary little-endian PLY, the layout ``plyfile`` writes)."""
+    from ..map_io import write_mesh_to_ply as _w
+    _w(v, f, ply_filename_out)

@@ -136,3 +136,22 @@ def test_two_extractors_share_one_decoder(decoder_state):
     ma, mb, ma2 = a.extract_mesh_from_code(z), b.extract_mesh_from_code(z), a.extract_mesh_from_code(z)
     assert np.array_equal(ma.vertices, ma2.vertices) and np.array_equal(ma.faces, ma2.faces)
     assert mb.vertices.shape[0] > ma.vertices.shape[0]
+
+
+def test_convert_sdf_voxels_to_mesh_and_ply(decoder_state, tmp_path):
+    """The reference's names for the last two steps (utils.py:120-164): isosurface of a decoded grid, PLY on disk."""
+    from qsp_slam_b200.decoder import DeviceDecoder
+    from qsp_slam_b200.reconstruct.optimizer import MeshExtractor
+    from qsp_slam_b200.reconstruct.utils import convert_sdf_voxels_to_mesh, write_mesh_to_ply
+    from qsp_slam_b200.map_io import read_ply
+    mx = MeshExtractor(DeviceDecoder(decoder_state, 0), 64, 32)
+    z = np.zeros(64, np.float32)
+    grid = mx.decode_grid(z)
+    v, f = convert_sdf_voxels_to_mesh(torch.from_numpy(grid))
+    m = mx.extract_mesh_from_code(z)
+    assert np.array_equal(v, m.vertices) and np.array_equal(f, m.faces)
+    vc, fc = convert_sdf_voxels_to_mesh(torch.from_numpy(grid).cuda())
+    assert np.array_equal(vc, v) and np.array_equal(fc, f)
+    write_mesh_to_ply(v, f, str(tmp_path / "m.ply"))
+    v2, f2 = read_ply(str(tmp_path / "m.ply"))
+    assert np.array_equal(v2, v) and np.array_equal(f2, f)

@@ -429,3 +429,26 @@ def test_depth_sample_counts_across_phase_boundaries(golden, dev, orc, samples):
     assert np.abs(it["H"] - o["H"].numpy()).max() < 5e-4 * np.abs(o["H"].numpy()).max()
     assert np.abs(it["b"] - o["b"].numpy()).max() < 1e-3 * np.abs(o["b"].numpy()).max()
     assert np.abs(it["dx"] - o["dx"].numpy()).max() < 3e-3 * np.abs(o["dx"].numpy()).max()
+
+
+def test_loss_utils_entry_points_keep_the_reference_signatures(golden, dev):
+    """decode_sdf / get_batch_sdf_jacobian under their reference names (loss_utils.py:51-103): argument order, result
+    shapes ((N,), (N,1,1), (N,1,67)) and values against the unmodified reference's outputs; numpy, CPU-tensor and
+    CUDA-tensor inputs."""
+    from qsp_slam_b200.reconstruct import loss_utils as LU
+    z, x = golden["dec_z"], golden["dec_x"]
+    s = LU.decode_sdf(dev, z, x)
+    assert isinstance(s, np.ndarray) and s.shape == (x.shape[0],)
+    assert np.abs(s - golden["dec_sdf"]).max() < 3e-5
+    st = LU.decode_sdf(dev, torch.from_numpy(z), torch.from_numpy(x))
+    assert isinstance(st, torch.Tensor) and not st.is_cuda and np.array_equal(st.numpy(), s)
+    sc = LU.decode_sdf(dev, torch.from_numpy(z).cuda(), torch.from_numpy(x).cuda())
+    assert sc.is_cuda and sc.shape == (x.shape[0],) and np.array_equal(sc.cpu().numpy(), s)
+    y, g = LU.get_batch_sdf_jacobian(dev, torch.from_numpy(z).cuda(), torch.from_numpy(x).cuda(), 1)
+    assert y.is_cuda and y.shape == (x.shape[0], 1, 1) and g.shape == (x.shape[0], 1, 67)
+    assert np.abs(y.cpu().numpy().reshape(-1) - golden["dec_jac_sdf"]).max() < 3e-5
+    assert rows_close(g.cpu().numpy()[:, 0], golden["dec_jac"], 1e-4)
+    yn, gn = LU.get_batch_sdf_jacobian(dev, z, x)
+    assert yn.shape == (x.shape[0], 1, 1) and np.array_equal(gn, g.cpu().numpy())
+    with pytest.raises(ValueError):
+        LU.get_batch_sdf_jacobian(dev, z, x, 2)
