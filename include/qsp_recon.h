@@ -79,6 +79,11 @@ int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_decoder** o
 void qsp_decoder_destroy(qsp_decoder* dec);
 
 int qsp_set_precision(qsp_decoder* dec, int32_t precision);
+/* Margin of the fp16 first pass (TENSOR precision): a ray sample / grid point whose first-pass |sdf| is below
+ * cut_off + margin0 + margin_per_norm * |code| is re-evaluated with fp32-equivalent arithmetic.  The defaults
+ * (0.0045, 0.004) stay 1.5x above the largest first-pass error seen over 72 M rows of three random-init decoders;
+ * a decoder with larger activations may need more (the result is exact as long as the error stays below it).    */
+int qsp_set_first_pass_margin(qsp_decoder* dec, float margin0, float margin_per_norm);
 
 /* --- kernel (a), forward only: replaces reconstruct/loss_utils.py:51-79 decode_sdf ----------- */
 /* out[c*n + i] = sdf(codes[c], pts[i]);  codes (n_codes,64), pts (n,3), out (n_codes,n).       */

@@ -69,6 +69,7 @@ struct qsp_decoder {
   int pair_grid = 148;
   int cluster = 2;                                 // CTAs per cluster sharing a multicast weight stream
   int t3_grid = 148;
+  float margin0 = QSP_FAST_MARGIN0, margin1 = QSP_FAST_MARGIN_PER_NORM;   // first-pass margin = margin0 + margin1 * |code|
   bool phases = true;                              // first pass front to back in phases of 32 samples per ray
   bool timeline = false;                           // QSP_TIMELINE=1: CUDA-event time of every launch group of one GN iteration
 };
@@ -342,6 +343,13 @@ extern "C" void qsp_decoder_destroy(qsp_decoder* d) {
 extern "C" int qsp_set_precision(qsp_decoder* d, int32_t precision) {
   if (!d || (precision != QSP_PREC_TENSOR && precision != QSP_PREC_FP32_CORES)) { g_err = "bad precision"; return QSP_ERR_INVALID; }
   d->precision = precision;
+  return QSP_OK;
+}
+
+extern "C" int qsp_set_first_pass_margin(qsp_decoder* d, float margin0, float margin_per_norm) {
+  if (!d || !(margin0 >= 0.f) || !(margin_per_norm >= 0.f)) { g_err = "bad argument"; return QSP_ERR_INVALID; }
+  d->margin0 = margin0;
+  d->margin1 = margin_per_norm;
   return QSP_OK;
 }
 
@@ -659,8 +667,8 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
 
   // first pass over the ray samples: single-pass fp16 tensor kernel + margin, or the exact kernel
   const int first_mode = d->precision == QSP_PREC_FP32_CORES ? DEC_FP32 : DEC_FAST;
-  const float margin0 = first_mode == DEC_FAST ? QSP_FAST_MARGIN0 : 0.f;
-  const float margin1 = first_mode == DEC_FAST ? QSP_FAST_MARGIN_PER_NORM : 0.f;
+  const float margin0 = first_mode == DEC_FAST ? d->margin0 : 0.f;
+  const float margin1 = first_mode == DEC_FAST ? d->margin1 : 0.f;
   const int cand_blocks = (int)((bandcap + tb - 1) / tb);
   CK(cudaMemsetAsync(counters, 0, (8 + GN_MAXC) * sizeof(int), st));
   int* phase_cnt = counters + 8;
@@ -1017,7 +1025,7 @@ extern "C" int qsp_extract_mesh(qsp_decoder* d, const float* code, float level, 
       CK(cudaStreamSynchronize(st));
       for (int c = 0; c < 64; ++c) zz += hc[c] * hc[c];
     }
-    const float margin = QSP_FAST_MARGIN0 + QSP_FAST_MARGIN_PER_NORM * std::sqrt(zz);
+    const float margin = d->margin0 + d->margin1 * std::sqrt(zz);
     const int tb = 256;
     if ((r = launch_decoder(d, DEC_FAST, false, pts, nullptr, dcode, 64, (long)V, nullptr, 1, sdf, nullptr, st))) return r;
     CK(cudaMemsetAsync(need, 0, V, st));

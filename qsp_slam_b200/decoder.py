@@ -85,6 +85,12 @@ class DeviceDecoder:
         or "fp32" (exact-fp32 CUDA-core kernel, for validation)."""
         N.check(N.lib().qsp_set_precision(self.handle, {"tensor": N.PREC_TENSOR, "fp32": N.PREC_FP32_CORES}[precision]))
 
+    def set_first_pass_margin(self, margin0: float = 0.0045, margin_per_norm: float = 0.004):
+        """Samples whose fp16 first-pass |sdf| is below cut_off + margin0 + margin_per_norm * |code| are re-evaluated
+        with fp32-equivalent arithmetic (GN loop and mesh extraction); results are exact while the first-pass error
+        stays below the margin."""
+        N.check(N.lib().qsp_set_first_pass_margin(self.handle, float(margin0), float(margin_per_norm)))
+
     def decode_sdf(self, codes, pts, mode: str = "tensor") -> np.ndarray:
         """codes (C,64) or (64,), pts (n,3) host arrays -> (C,n) or (n,) float32  (loss_utils.py:51-79).
         mode: "tensor" (fp16-pair tensor-core kernel), "fast" (single-pass fp16), "fp32" (CUDA cores)."""

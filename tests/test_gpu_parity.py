@@ -452,3 +452,28 @@ def test_loss_utils_entry_points_keep_the_reference_signatures(golden, dev):
     assert yn.shape == (x.shape[0], 1, 1) and np.array_equal(gn, g.cpu().numpy())
     with pytest.raises(ValueError):
         LU.get_batch_sdf_jacobian(dev, z, x, 2)
+
+
+def test_first_pass_margin_only_changes_the_amount_of_exact_work(golden, decoder_state):
+    """A wider first-pass margin re-evaluates more samples exactly; the kept band points (and their order) are the
+    same, so the results agree to fp32 summation order.  Negative margins are rejected."""
+    from qsp_slam_b200.decoder import DeviceDecoder
+    p = "kitti0_"
+    res = []
+    for m0, m1 in ((0.0045, 0.004), (0.012, 0.01)):
+        d = DeviceDecoder(decoder_state, 0)
+        d.set_first_pass_margin(m0, m1)
+        opt = make_opt(d, "kitti", 2)
+        opt.set_debug(True)
+        out = opt.reconstruct_object(golden[p + "t_cam_obj"], golden[p + "pts"], golden[p + "rays"],
+                                     golden[p + "depth"], golden[p + "code0"])
+        res.append((out, opt.get_iteration(1)))
+    (o0, i0), (o1, i1) = res
+    assert i1["n_cand"] > i0["n_cand"] and i1["n_first_pass"] >= i0["n_first_pass"]
+    assert i1["n_keep"] == i0["n_keep"] and np.array_equal(i1["keep_ray"], i0["keep_ray"])
+    assert np.array_equal(i1["keep_sample"], i0["keep_sample"])
+    # sums run over the same kept rows, but the rows sit at other positions of the chunks: fp32 summation order
+    assert np.abs(i1["dx"] - i0["dx"]).max() < 1e-4 * np.abs(i0["dx"]).max()
+    assert np.abs(o1.t_cam_obj - o0.t_cam_obj).max() < 1e-5 and np.abs(o1.code - o0.code).max() < 1e-5
+    with pytest.raises(Exception):
+        DeviceDecoder(decoder_state, 0).set_first_pass_margin(-1.0, 0.0)
