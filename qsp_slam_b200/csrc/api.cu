@@ -29,6 +29,26 @@ static std::atomic<long long> g_launches{0};
   } while (0)
 #define LAUNCHED() (g_launches.fetch_add(1, std::memory_order_relaxed))
 
+// Programmatic dependent launch for the kernels that start with pdl_prologue() (common.cuh); QSP_PDL=0 turns the
+// launch attribute off (plain stream order, same results).
+static const bool g_pdl = !(getenv("QSP_PDL") && atoi(getenv("QSP_PDL")) == 0);
+
+template <typename... KArgs, typename... Args>
+static cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = g_pdl ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+#define KL(kernel, grid, block, st, ...)                                                \
+  do {                                                                                  \
+    CK(launch_k(kernel, dim3(grid), dim3(block), 0, st, __VA_ARGS__));                  \
+    LAUNCHED();                                                                         \
+  } while (0)
+
 struct Buf {
   void* p = nullptr;
   size_t bytes = 0;
@@ -374,10 +394,12 @@ static int launch_clustered(K kernel, int grid, int cl, size_t smem, cudaStream_
   cfg.blockDim = dim3(TC_THREADS);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
-  cudaLaunchAttribute at[1];
+  cudaLaunchAttribute at[2];
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = cl; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-  cfg.attrs = at; cfg.numAttrs = 1;
+  at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = g_pdl ? 2 : 1;
   CK(cudaLaunchKernelEx(&cfg, kernel, tc, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp));
   return QSP_OK;
 }
@@ -451,9 +473,9 @@ static int launch_decoder(qsp_decoder* d, int mode, bool jac, const float* pts, 
   DecoderDev dw = d->dw;
   dw.row_map = row_map;
   if (jac)
-    k_decoder_ffma<true><<<grid, FF_THREADS, FF_SMEM_BYTES, st>>>(dw, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
+    CK(launch_k(k_decoder_ffma<true>, grid, dim3(FF_THREADS), FF_SMEM_BYTES, st, dw, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp));
   else
-    k_decoder_ffma<false><<<grid, FF_THREADS, FF_SMEM_BYTES, st>>>(dw, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
+    CK(launch_k(k_decoder_ffma<false>, grid, dim3(FF_THREADS), FF_SMEM_BYTES, st, dw, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp));
   LAUNCHED();
   CK(cudaGetLastError());
   return QSP_OK;
@@ -660,7 +682,7 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
   const int hp_mode = d->precision == QSP_PREC_FP32_CORES ? DEC_FP32 : DEC_SPLIT;
   k_fill_obj_map<<<B, 128, 0, st>>>(d_rays_off, B, ray_obj); LAUNCHED();
   k_fill_obj_map<<<B, 128, 0, st>>>(d_pts_off, B, pt_obj); LAUNCHED();
-  k_init_state<<<(B + 63) / 64, 64, 0, st>>>(state, in.T, in.codes, B); LAUNCHED();
+  KL(k_init_state, (B + 63) / 64, 64, st, state, in.T, in.codes, B);
   const int ray_blocks = std::max(1, (R * 32 + tb - 1) / tb);   // R == 0: every object fails the in-ball test (loss.py:73-74)
   const float* codes_dev = reinterpret_cast<const float*>(state) + offsetof(ObjState, code) / 4;
   const int code_stride = sizeof(ObjState) / 4;
@@ -685,18 +707,18 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
   } while (0)
   for (int it = 0; it < prm->num_iterations; ++it) {
     MARK("start");
-    k_prep<<<(B + 63) / 64, 64, 0, st>>>(state, B, S, phase_cnt, p.th, margin0, margin1); LAUNCHED();
+    KL(k_prep, (B + 63) / 64, 64, st, state, B, S, phase_cnt, p.th, margin0, margin1);
     MARK("k_prep");
     // (b) sample, in-ball test, ordered compaction
-    k_sample<false><<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, R, S, ray_cnt, nullptr, nullptr, nullptr, nullptr); LAUNCHED();
-    k_exclusive_scan<<<1, 1024, 0, st>>>(ray_cnt, ray_base, R, counters + 0, 0, nullptr); LAUNCHED();
-    k_sample<true><<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, R, S, nullptr, ray_base, q_pts, q_code, q_samp); LAUNCHED();
+    KL(k_sample<false>, ray_blocks, tb, st, state, in.rays, ray_obj, R, S, ray_cnt, nullptr, nullptr, nullptr, nullptr);
+    KL(k_exclusive_scan, 1, 1024, st, ray_cnt, ray_base, R, counters + 0, 0, nullptr);
+    KL(k_sample<true>, ray_blocks, tb, st, state, in.rays, ray_obj, R, S, nullptr, ray_base, q_pts, q_code, q_samp);
     MARK("k_sample x2 + scan");
     // (a) forward decode of the in-ball samples (loss.py:77-78), first pass
     // in phases of 32 samples along the ray; a ray stops at its first certainly-opaque sample (k_phase_list)
     if (d->phases) {
       for (int ph = 0; ph < n_phases; ++ph) {
-        k_phase_list<<<ray_blocks, tb, 0, st>>>(ph, R, state, ray_obj, ray_base, q_sdf, q_code, ray_nev, ph_list, ph_code, phase_cnt); LAUNCHED();
+        KL(k_phase_list, ray_blocks, tb, st, ph, R, state, ray_obj, ray_base, q_sdf, q_code, ray_nev, ph_list, ph_code, phase_cnt);
         MARK("k_phase_list");
         if ((r = launch_decoder(d, first_mode, false, q_pts, ph_code, codes_dev, code_stride, 0, phase_cnt + ph, 1, q_sdf, nullptr, st, ph_list))) return r;
         MARK("first-pass decoder");
@@ -706,28 +728,28 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
     }
     const int* nev = d->phases ? ray_nev : ray_cnt;     // decoded samples per ray
     // candidates near the band, appended behind the surface points in the Jacobian row list
-    k_candidates<false><<<ray_blocks, tb, 0, st>>>(state, ray_obj, ray_base, nev, R, q_sdf, band_cnt, nullptr, M, (int)bandcap, nullptr,
-                                                   nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr); LAUNCHED();
-    k_exclusive_scan<<<1, 1024, 0, st>>>(band_cnt, band_base, R, counters + 1, M, counters + 2); LAUNCHED();
-    k_candidates<true><<<ray_blocks, tb, 0, st>>>(state, ray_obj, ray_base, nev, R, q_sdf, nullptr, band_base, M, (int)bandcap, q_pts,
-                                                  q_code, q_samp, jp_pts, jp_code, row_ray, row_samp, cand_q, counters + 3); LAUNCHED();
-    k_surface_xform<<<std::max(1, (M + tb - 1) / tb), tb, 0, st>>>(state, in.pts, pt_obj, M, jp_pts, jp_code); LAUNCHED();
+    KL(k_candidates<false>, ray_blocks, tb, st, state, ray_obj, ray_base, nev, R, q_sdf, band_cnt, nullptr, M, (int)bandcap, nullptr,
+                                                   nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+    KL(k_exclusive_scan, 1, 1024, st, band_cnt, band_base, R, counters + 1, M, counters + 2);
+    KL(k_candidates<true>, ray_blocks, tb, st, state, ray_obj, ray_base, nev, R, q_sdf, nullptr, band_base, M, (int)bandcap, q_pts,
+                                                  q_code, q_samp, jp_pts, jp_code, row_ray, row_samp, cand_q, counters + 3);
+    KL(k_surface_xform, std::max(1, (M + tb - 1) / tb), tb, st, state, in.pts, pt_obj, M, jp_pts, jp_code);
     MARK("k_candidates x2 + scan + k_surface_xform");
     // (a) SDF + input Jacobian of surface points and candidates (loss.py:34,144), fp32-equivalent
     if ((r = launch_decoder(d, hp_mode, true, jp_pts, jp_code, codes_dev, code_stride, 0, counters + 2, 1, g_sdf, g_jac, st))) return r;
     MARK("fwd+Jacobian decoder");
-    k_refine_scatter<<<cand_blocks, tb, 0, st>>>(counters + 1, (int)bandcap, cand_q, g_sdf, M, q_sdf); LAUNCHED();
+    KL(k_refine_scatter, cand_blocks, tb, st, counters + 1, (int)bandcap, cand_q, g_sdf, M, q_sdf);
     // (b) occupancy, transmittance, rendered depth, band selection
-    k_render<<<ray_blocks, tb, 0, st>>>(state, in.rays, ray_obj, d_rays_off, in.depth, d_depth_off, R, S, p.th,
-                                        ray_base, q_sdf, nev, slot, ray_res, band_cnt); LAUNCHED();
-    k_row_factors<<<cand_blocks, tb, 0, st>>>(counters + 1, (int)bandcap, M, S, row_ray, row_samp, slot, ray_res,
-                                              row_fac, row_res); LAUNCHED();
+    KL(k_render, ray_blocks, tb, st, state, in.rays, ray_obj, d_rays_off, in.depth, d_depth_off, R, S, p.th,
+                                        ray_base, q_sdf, nev, slot, ray_res, band_cnt);
+    KL(k_row_factors, cand_blocks, tb, st, counters + 1, (int)bandcap, M, S, row_ray, row_samp, slot, ray_res,
+                                              row_fac, row_res);
     MARK("k_refine_scatter + k_render + k_row_factors");
     // (c) chain rule + normal equations, (d) solve + update
-    k_accumulate<<<dim3(nchunk, B, 2), 256, 0, st>>>(state, d_pts_off, d_rays_off, band_base, M, jp_pts, g_sdf, g_jac,
-                                                     row_fac, row_res, p.b2, p.b1, 0, nullptr, partials); LAUNCHED();
+    KL(k_accumulate, dim3(nchunk, B, 2), 256, st, state, d_pts_off, d_rays_off, band_base, M, jp_pts, g_sdf, g_jac,
+                                                     row_fac, row_res, p.b2, p.b1, 0, nullptr, partials);
     MARK("k_accumulate");
-    k_solve<<<B, 256, 0, st>>>(state, d_pts_off, nchunk, partials, p, 0, nullptr, dbgH, dbgb, dbgdx); LAUNCHED();
+    KL(k_solve, B, 256, st, state, d_pts_off, nchunk, partials, p, 0, nullptr, dbgH, dbgb, dbgdx);
     MARK("k_solve");
     CK(cudaGetLastError());
     if (d->debug) {  // parity inspection: copy this iteration's normal equations and index lists out
@@ -762,7 +784,7 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
     }
   }
 #undef MARK
-  k_finalize<<<(B + 63) / 64, 64, 0, st>>>(state, B, d_rec); LAUNCHED();
+  KL(k_finalize, (B + 63) / 64, 64, st, state, B, d_rec);
   CK(cudaGetLastError());
   if (!marks.empty()) {
     CK(cudaStreamSynchronize(st));
@@ -862,22 +884,22 @@ extern "C" int qsp_estimate_pose_batch(qsp_decoder* d, int32_t num_iterations, i
   const int tb = 256;
   GnParamsDev p{};
   k_fill_obj_map<<<B, 128, 0, st>>>(d_pts_off, B, pt_obj); LAUNCHED();
-  k_init_pose_only<<<(B + 63) / 64, 64, 0, st>>>(state, in.T, in.scale, in.codes, B); LAUNCHED();
+  KL(k_init_pose_only, (B + 63) / 64, 64, st, state, in.T, in.scale, in.codes, B);
   k_fill_float<<<std::max(1, (M + tb - 1) / tb), tb, 0, st>>>(row_active, M, 1.f); LAUNCHED();
   k_count_active<<<(B + 63) / 64, 64, 0, st>>>(d_pts_off, B, m_active); LAUNCHED();
   const float* codes_dev = reinterpret_cast<const float*>(state) + offsetof(ObjState, code) / 4;
   for (int it = 0; it < num_iterations; ++it) {
-    k_surface_xform<<<std::max(1, (M + tb - 1) / tb), tb, 0, st>>>(state, in.pts, pt_obj, M, jp_pts, jp_code); LAUNCHED();
+    KL(k_surface_xform, std::max(1, (M + tb - 1) / tb), tb, st, state, in.pts, pt_obj, M, jp_pts, jp_code);
     if ((r = launch_decoder(d, d->precision == QSP_PREC_FP32_CORES ? DEC_FP32 : DEC_SPLIT, true, jp_pts, jp_code, codes_dev, sizeof(ObjState) / 4, M, nullptr, 1, g_sdf, g_jac, st))) return r;
-    k_accumulate<<<dim3(nchunk, B, 1), 256, 0, st>>>(state, d_pts_off, d_pts_off, nullptr, M, jp_pts, g_sdf, g_jac,
-                                                     nullptr, nullptr, 0.f, 0.f, 1, row_active, partials); LAUNCHED();
-    k_solve<<<B, 256, 0, st>>>(state, d_pts_off, nchunk, partials, p, 1, m_active, nullptr, nullptr, nullptr); LAUNCHED();
+    KL(k_accumulate, dim3(nchunk, B, 1), 256, st, state, d_pts_off, d_pts_off, nullptr, M, jp_pts, g_sdf, g_jac,
+                                                     nullptr, nullptr, 0.f, 0.f, 1, row_active, partials);
+    KL(k_solve, B, 256, st, state, d_pts_off, nchunk, partials, p, 1, m_active, nullptr, nullptr, nullptr);
     if (it == 4) {  // optimizer.py:80-82
       CK(cudaMemsetAsync(m_active, 0, (size_t)B * 4, st));
-      k_prune<<<std::max(1, (M + tb - 1) / tb), tb, 0, st>>>(g_sdf, pt_obj, M, row_active, m_active); LAUNCHED();
+      KL(k_prune, std::max(1, (M + tb - 1) / tb), tb, st, g_sdf, pt_obj, M, row_active, m_active);
     }
   }
-  k_finalize_pose_only<<<(B + 63) / 64, 64, 0, st>>>(state, in.scale, B, d_out); LAUNCHED();
+  KL(k_finalize_pose_only, (B + 63) / 64, 64, st, state, in.scale, B, d_out);
   CK(cudaGetLastError());
   if (host) {
     CK(cudaMemcpyAsync(out, d_out, (size_t)B * 16 * 4, cudaMemcpyDeviceToHost, st));

@@ -51,6 +51,16 @@ struct GnParamsDev {
   int iters, S;
 };
 
+// Programmatic dependent launch (launches carrying cudaLaunchAttributeProgrammaticStreamSerialization): let the next
+// kernel of the stream be scheduled right away, then wait until the previous kernel has completed and its memory
+// is visible.  Every kernel of the GN loop starts with this, so execution order and results are those of plain
+// stream order while the launch latencies of the ~22 small kernels per iteration overlap with their predecessors.
+// A no-op for launches without the attribute.
+__device__ __forceinline__ void pdl_prologue() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

@@ -30,6 +30,7 @@ k_decoder_ffma(DecoderDev dw, const float* __restrict__ pts, const int* __restri
                const float* __restrict__ codes, int code_stride, int n_codes, long n_host,
                const int* __restrict__ n_dev,
                float* __restrict__ sdf_out, float* __restrict__ jac_out) {
+  pdl_prologue();                                       // see common.cuh: stream order is kept
   extern __shared__ __align__(16) float smem[];
   float* act = smem;                                  // [64][512]
   float* wt = smem + FF_TILE * QSP_HID;               // [2][16][512]

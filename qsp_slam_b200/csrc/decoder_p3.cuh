@@ -29,6 +29,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
 k_decoder_p3(TcDecoderDev dw, const float* __restrict__ pts, const int* __restrict__ code_idx,
              const float* __restrict__ codes, int code_stride, int n_codes, long n_host,
              const int* __restrict__ n_dev, float* __restrict__ sdf_out, float* __restrict__ jac_out) {
+  pdl_prologue();                                       // see common.cuh: stream order is kept
   static_assert(TC_NG == 2, "the epilogue mapping is written for 8 epilogue warps");
   constexpr int NSTEPS = JAC ? 16 : 8;
   constexpr int NST = 2 * TC_STAGES;                     // ring stages of 16 KB: this CTA's [128 n][64 k] half tile

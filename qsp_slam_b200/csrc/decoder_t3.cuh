@@ -59,6 +59,7 @@ __global__ void __launch_bounds__(T3_THREADS, 1)
 k_decoder_t3(TcDecoderDev dw, const float* __restrict__ pts, const int* __restrict__ code_idx,
              const float* __restrict__ codes, int code_stride, int n_codes, long n_host,
              const int* __restrict__ n_dev, float* __restrict__ sdf_out, float* __restrict__ jac_out) {
+  pdl_prologue();                                       // see common.cuh: stream order is kept
   static_assert(T3_EPI == 256, "the epilogue mapping assumes 8 epilogue warps");
   constexpr int NSTEPS = JAC ? 16 : 8;
   extern __shared__ __align__(1024) uint8_t smem_raw[];

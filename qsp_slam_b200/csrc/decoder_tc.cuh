@@ -97,6 +97,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1)
 k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restrict__ code_idx,
              const float* __restrict__ codes, int code_stride, int n_codes, long n_host,
              const int* __restrict__ n_dev, float* __restrict__ sdf_out, float* __restrict__ jac_out) {
+  pdl_prologue();                                       // see common.cuh: stream order is kept
   static_assert(!(JAC && MODE == TC_FAST), "the reverse sweep exists only in split mode");
   constexpr int ROWS = MODE == TC_SPLIT ? 64 : 128;      // points per tile
   constexpr int TPB = MODE == TC_SPLIT ? 2 : 1;          // weight tiles per (half, k-block)

@@ -63,6 +63,7 @@ __device__ __forceinline__ bool in_ball(float x, float y, float z) {
 // ------------------------------------------------------------------------------------------------
 __global__ void k_init_state(ObjState* st, const float* __restrict__ t_cam_obj,
                              const float* __restrict__ codes_in, int B) {
+  pdl_prologue();
   int o = blockIdx.x * blockDim.x + threadIdx.x;
   if (o >= B) return;
   ObjState& s = st[o];
@@ -76,6 +77,7 @@ __global__ void k_init_state(ObjState* st, const float* __restrict__ t_cam_obj,
 // depth range, background depth and rotation prior of the current pose (optimizer.py:144-153,
 // loss.py:155-178)
 __global__ void k_prep(ObjState* st, int B, int S, int* phase_cnt, float th, float margin0, float margin_per_norm) {
+  pdl_prologue();
   int o = blockIdx.x * blockDim.x + threadIdx.x;
   if (phase_cnt && o < GN_MAXC) phase_cnt[o] = 0;      // row counts of this iteration's first-pass phases
   if (o >= B) return;
@@ -134,6 +136,7 @@ __global__ void k_sample(const ObjState* __restrict__ st, const float* __restric
                          const int* __restrict__ ray_obj, int R, int S, int* __restrict__ ray_cnt,
                          const int* __restrict__ ray_base, float* __restrict__ q_pts, int* __restrict__ q_code,
                          int* __restrict__ q_samp) {
+  pdl_prologue();
   int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (r >= R) return;
   int o = ray_obj[r];
@@ -173,6 +176,7 @@ __global__ void k_phase_list(int p, int R, const ObjState* __restrict__ st, cons
                              const int* __restrict__ ray_base, const float* __restrict__ q_sdf,
                              const int* __restrict__ q_code, int* __restrict__ ray_nev,
                              int* __restrict__ list, int* __restrict__ list_code, int* __restrict__ phase_cnt) {
+  pdl_prologue();
   int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (r >= R) return;
   const int lo = ray_base[r], n = ray_base[r + 1] - lo, start = p * 32;
@@ -198,6 +202,7 @@ __global__ void k_phase_list(int p, int R, const ObjState* __restrict__ st, cons
 // exclusive scan of n ints into out[0..n] (out[n] = total); single block, fixed order
 __global__ void k_exclusive_scan(const int* __restrict__ in, int* __restrict__ out, int n,
                                  int* total, int total_add, int* total2) {
+  pdl_prologue();
   __shared__ int wsum[32];
   __shared__ int carry_s;
   int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -245,6 +250,7 @@ __global__ void k_render(ObjState* __restrict__ st, const float* __restrict__ ra
                          int R, int S, float th, const int* __restrict__ ray_base,
                          const float* __restrict__ q_sdf, const int* __restrict__ ray_nev,
                          float* __restrict__ slot_de_ds, float* __restrict__ ray_res, int* __restrict__ band_cnt) {
+  pdl_prologue();
   int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (r >= R) return;
   int o = ray_obj[r];
@@ -351,6 +357,7 @@ __global__ void k_band_fill(const ObjState* __restrict__ st, const float* __rest
                             const int* __restrict__ band_base, int row0, float* __restrict__ jp_pts,
                             int* __restrict__ jp_code, float* __restrict__ row_fac,
                             float* __restrict__ row_res, int* __restrict__ row_ray, int* __restrict__ row_samp) {
+  pdl_prologue();
   int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (r >= R) return;
   int o = ray_obj[r];
@@ -382,6 +389,7 @@ __global__ void k_band_fill(const ObjState* __restrict__ st, const float* __rest
 __global__ void k_surface_xform(const ObjState* __restrict__ st, const float* __restrict__ pts,
                                 const int* __restrict__ pt_obj, int M, float* __restrict__ jp_pts,
                                 int* __restrict__ jp_code) {
+  pdl_prologue();
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= M) return;
   int o = pt_obj[i];
@@ -413,6 +421,7 @@ k_accumulate(const ObjState* __restrict__ st, const int* __restrict__ pts_off,
              const float* __restrict__ g_jac, const float* __restrict__ row_fac,
              const float* __restrict__ row_res, float b_sdf, float b_render, int pose_only,
              const float* __restrict__ row_active, float* __restrict__ partials) {
+  pdl_prologue();
   __shared__ __align__(16) float J[GN_SLOT][72];
   const int chunk = blockIdx.x, nchunk = gridDim.x, o = blockIdx.y, term = blockIdx.z;
   const int tid = threadIdx.x;
@@ -558,6 +567,7 @@ __global__ void __launch_bounds__(256)
 k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
         const float* __restrict__ partials, GnParamsDev p, int pose_only,
         const int* __restrict__ m_active, float* __restrict__ dbg_H, float* __restrict__ dbg_b, float* __restrict__ dbg_dx) {
+  pdl_prologue();
   __shared__ double A[72][73];
   __shared__ double rhs[72];
   __shared__ float dxs[72];
@@ -752,6 +762,7 @@ k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
 
 // records: t_cam_obj (16) | code (64) | is_good | loss  (optimizer.py:274-281)
 __global__ void k_finalize(const ObjState* __restrict__ st, int B, float* __restrict__ records) {
+  pdl_prologue();
   int o = blockIdx.x * blockDim.x + threadIdx.x;
   if (o >= B) return;
   const ObjState& s = st[o];
@@ -768,6 +779,7 @@ __global__ void k_finalize(const ObjState* __restrict__ st, int B, float* __rest
 // inlier pruning of the pose-only loop: keep |res| <= 0.05 after iteration index 4 (optimizer.py:80-82)
 __global__ void k_prune(const float* __restrict__ g_sdf, const int* __restrict__ pt_obj, int M,
                         float* __restrict__ row_active, int* __restrict__ m_active) {
+  pdl_prologue();
   int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= M) return;
   bool keep = row_active[i] != 0.f && fabsf(g_sdf[i]) <= 0.05f;
@@ -778,6 +790,7 @@ __global__ void k_prune(const float* __restrict__ g_sdf, const int* __restrict__
 // pose-only set-up: T_oc = inverse([scale * R | t]) (optimizer.py:57-59); result conversion (:87-88)
 __global__ void k_init_pose_only(ObjState* st, const float* __restrict__ t_co_se3,
                                  const float* __restrict__ scale, const float* __restrict__ codes, int B) {
+  pdl_prologue();
   int o = blockIdx.x * blockDim.x + threadIdx.x;
   if (o >= B) return;
   float T[16];
@@ -791,6 +804,7 @@ __global__ void k_init_pose_only(ObjState* st, const float* __restrict__ t_co_se
 }
 __global__ void k_finalize_pose_only(const ObjState* __restrict__ st, const float* __restrict__ scale,
                                      int B, float* __restrict__ out) {
+  pdl_prologue();
   int o = blockIdx.x * blockDim.x + threadIdx.x;
   if (o >= B) return;
   float T[16];
@@ -816,6 +830,7 @@ __global__ void k_candidates(const ObjState* __restrict__ st, const int* __restr
                              const int* __restrict__ q_samp, float* __restrict__ jp_pts, int* __restrict__ jp_code,
                              int* __restrict__ row_ray, int* __restrict__ row_samp, int* __restrict__ cand_q,
                              int* __restrict__ overflow) {
+  pdl_prologue();
   int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (r >= R) return;
   const int lo = ray_base[r], hi = lo + ray_nev[r];     // the decoded samples of the ray (k_phase_list)
@@ -854,6 +869,7 @@ __global__ void k_candidates(const ObjState* __restrict__ st, const int* __restr
 // exact SDF of the candidates back into the per-sample list read by k_render
 __global__ void k_refine_scatter(const int* __restrict__ n_cand, int cap, const int* __restrict__ cand_q,
                                  const float* __restrict__ g_sdf, int row0, float* __restrict__ q_sdf) {
+  pdl_prologue();
   int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= min(*n_cand, cap)) return;
   q_sdf[cand_q[k]] = g_sdf[row0 + k];
@@ -865,6 +881,7 @@ __global__ void k_row_factors(const int* __restrict__ n_cand, int cap, int row0,
                               const int* __restrict__ row_ray, const int* __restrict__ row_samp,
                               const float* __restrict__ slot_de_ds, const float* __restrict__ ray_res,
                               float* __restrict__ row_fac, float* __restrict__ row_res) {
+  pdl_prologue();
   int k = blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= min(*n_cand, cap)) return;
   int row = row0 + k, r = row_ray[row];
