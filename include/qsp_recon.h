@@ -84,6 +84,13 @@ int qsp_set_precision(qsp_decoder* dec, int32_t precision);
  * (0.0045, 0.004) stay 1.5x above the largest first-pass error seen over 72 M rows of three random-init decoders;
  * a decoder with larger activations may need more (the result is exact as long as the error stays below it).    */
 int qsp_set_first_pass_margin(qsp_decoder* dec, float margin0, float margin_per_norm);
+/* Debug aid (no reference counterpart).  With QSP_GUARD=1 in the environment every workspace buffer of the handle is
+ * allocated at exactly the size the call asked for, between two 256-byte canary bands.  This call synchronises the
+ * device and returns how many buffers had a band overwritten (names in qsp_last_error()), 0 if none, -1 if the
+ * handle holds no guarded buffer.                                                                              */
+int qsp_check_guards(qsp_decoder* dec);
+/* Positive control for the above: writes one byte just past the first guarded buffer of the handle. */
+int qsp_guard_selftest(qsp_decoder* dec);
 
 /* --- kernel (a), forward only: replaces reconstruct/loss_utils.py:51-79 decode_sdf ----------- */
 /* out[c*n + i] = sdf(codes[c], pts[i]);  codes (n_codes,64), pts (n,3), out (n_codes,n).       */

@@ -5,7 +5,9 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/qsp_recon.h"
@@ -52,7 +54,15 @@ static cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, siz
 struct Buf {
   void* p = nullptr;
   size_t bytes = 0;
+  void* raw = nullptr;                 // allocation base; differs from p only in guard mode (QSP_GUARD=1)
+  bool guarded = false;
 };
+// QSP_GUARD=1 (debug): every workspace buffer is allocated at exactly the requested size between two 256-byte
+// canary bands, and qsp_check_guards() reports the buffers whose bands were written.  compute-sanitizer's memcheck
+// for boxes that do not allow it.
+constexpr size_t GUARD_BYTES = 256;
+constexpr int GUARD_FILL = 0xA5;
+static bool guard_mode() { const char* e = getenv("QSP_GUARD"); return e && atoi(e) != 0; }
 
 struct IterDebug {
   std::vector<float> H, b, dx;         // (B,71,71), (B,71), (B,71)
@@ -98,16 +108,32 @@ template <typename T>
 static int ensure(Buf& b, size_t n, T** out) {
   size_t need = n * sizeof(T);
   if (need == 0) need = sizeof(T);
-  if (b.bytes < need) {
-    if (b.p) cudaFree(b.p);
-    b.p = nullptr;
+  const bool guard = guard_mode();
+  if (b.bytes < need || guard != b.guarded) {
+    if (b.raw) cudaFree(b.raw);
+    b.p = b.raw = nullptr;
     b.bytes = 0;
-    size_t cap = need + need / 4 + 256;
-    if (cudaMalloc(&b.p, cap) != cudaSuccess) {
-      g_err = "cudaMalloc failed";
-      return QSP_ERR_ALLOC;
+    b.guarded = false;
+    if (guard) {
+      size_t cap = (need + 15) & ~(size_t)15;
+      if (cudaMalloc(&b.raw, cap + 2 * GUARD_BYTES) != cudaSuccess) {
+        g_err = "cudaMalloc failed";
+        return QSP_ERR_ALLOC;
+      }
+      b.p = static_cast<char*>(b.raw) + GUARD_BYTES;
+      cudaMemset(b.raw, GUARD_FILL, GUARD_BYTES);
+      cudaMemset(static_cast<char*>(b.p) + cap, GUARD_FILL, GUARD_BYTES);
+      b.bytes = cap;
+      b.guarded = true;
+    } else {
+      size_t cap = need + need / 4 + 256;
+      if (cudaMalloc(&b.raw, cap) != cudaSuccess) {
+        g_err = "cudaMalloc failed";
+        return QSP_ERR_ALLOC;
+      }
+      b.p = b.raw;
+      b.bytes = cap;
     }
-    b.bytes = cap;
   }
   *out = reinterpret_cast<T*>(b.p);
   return QSP_OK;
@@ -341,20 +367,68 @@ extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_
   return QSP_OK;
 }
 
+
+#define NB(name) {#name, &d->name}
+static std::vector<std::pair<const char*, Buf*>> all_bufs(qsp_decoder* d) {
+  return {NB(in_T), NB(in_code), NB(in_pts), NB(in_rays), NB(in_depth), NB(in_scale), NB(out_rec), NB(pts_off),
+          NB(rays_off), NB(depth_off), NB(ray_obj), NB(pt_obj), NB(state), NB(counters), NB(ray_cnt), NB(ray_base),
+          NB(band_cnt), NB(band_base), NB(q_pts), NB(q_code), NB(q_samp), NB(cand_q), NB(q_sdf), NB(slot), NB(ray_res),
+          NB(ray_nev), NB(ph_list), NB(ph_code), NB(grid_pts), NB(grid_sdf), NB(grid_need), NB(grid_list), NB(grid_cnt),
+          NB(grid_code), NB(jp_pts), NB(jp_code), NB(g_sdf), NB(g_jac), NB(row_fac), NB(row_res), NB(row_ray),
+          NB(row_samp), NB(row_active), NB(m_active), NB(partials), NB(dbgH), NB(dbgb), NB(dbgdx), NB(dec_pts),
+          NB(dec_codes), NB(dec_out), NB(dec_jac)};
+}
+#undef NB
+
+// Debug (QSP_GUARD=1): synchronises the device and returns the number of workspace buffers whose canary bands were
+// overwritten (their names in qsp_last_error()), 0 if all are intact, -1 if no buffer is guarded.
+extern "C" int qsp_check_guards(qsp_decoder* d) {
+  if (!d) { g_err = "null handle"; return QSP_ERR_INVALID; }
+  cudaSetDevice(d->device);
+  if (cudaDeviceSynchronize() != cudaSuccess) { g_err = "cudaDeviceSynchronize failed"; return QSP_ERR_CUDA; }
+  int bad = 0, seen = 0;
+  std::string names;
+  std::vector<unsigned char> h(2 * GUARD_BYTES);
+  for (auto& nb : all_bufs(d)) {
+    Buf* b = nb.second;
+    if (!b->guarded || !b->raw) continue;
+    ++seen;
+    cudaMemcpy(h.data(), b->raw, GUARD_BYTES, cudaMemcpyDeviceToHost);
+    cudaMemcpy(h.data() + GUARD_BYTES, static_cast<char*>(b->p) + b->bytes, GUARD_BYTES, cudaMemcpyDeviceToHost);
+    bool lo = false, hi = false;
+    for (size_t i = 0; i < GUARD_BYTES; ++i) {
+      lo |= h[i] != GUARD_FILL;
+      hi |= h[GUARD_BYTES + i] != GUARD_FILL;
+    }
+    if (lo || hi) {
+      ++bad;
+      names += std::string(names.empty() ? "" : ", ") + nb.first + (lo ? " (below)" : "") + (hi ? " (above)" : "");
+    }
+  }
+  if (bad) g_err = "guard bands overwritten: " + names;
+  return seen ? bad : -1;
+}
+
+// Debug: positive control for qsp_check_guards - writes one byte just past the first guarded buffer.
+extern "C" int qsp_guard_selftest(qsp_decoder* d) {
+  if (!d) { g_err = "null handle"; return QSP_ERR_INVALID; }
+  cudaSetDevice(d->device);
+  for (auto& nb : all_bufs(d)) {
+    Buf* b = nb.second;
+    if (!b->guarded || !b->raw) continue;
+    CK(cudaMemset(static_cast<char*>(b->p) + b->bytes, 0, 1));
+    return QSP_OK;
+  }
+  g_err = "no guarded buffer";
+  return QSP_ERR_INVALID;
+}
+
 extern "C" void qsp_decoder_destroy(qsp_decoder* d) {
   if (!d) return;
   cudaSetDevice(d->device);
   for (void* p : d->weight_allocs) cudaFree(p);
-  Buf* bufs[] = {&d->in_T, &d->in_code, &d->in_pts, &d->in_rays, &d->in_depth, &d->in_scale, &d->out_rec,
-                 &d->pts_off, &d->rays_off, &d->depth_off, &d->ray_obj, &d->pt_obj, &d->state, &d->counters,
-                 &d->ray_cnt, &d->ray_base, &d->band_cnt, &d->band_base, &d->q_pts, &d->q_code, &d->q_samp, &d->cand_q, &d->q_sdf,
-                 &d->slot, &d->ray_res, &d->jp_pts, &d->jp_code, &d->g_sdf, &d->g_jac, &d->row_fac,
-                 &d->row_res, &d->row_ray, &d->row_samp, &d->row_active, &d->m_active, &d->partials,
-                 &d->dbgH, &d->dbgb, &d->dbgdx, &d->dec_pts, &d->dec_codes, &d->dec_out, &d->dec_jac,
-                 &d->ray_nev, &d->ph_list, &d->ph_code, &d->grid_pts, &d->grid_sdf, &d->grid_need, &d->grid_list,
-                 &d->grid_cnt, &d->grid_code};
-  for (Buf* b : bufs)
-    if (b->p) cudaFree(b->p);
+  for (auto& nb : all_bufs(d))
+    if (nb.second->raw) cudaFree(nb.second->raw);
   if (d->ev0) cudaEventDestroy(d->ev0);
   if (d->ev1) cudaEventDestroy(d->ev1);
   delete d;

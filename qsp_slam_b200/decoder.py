@@ -91,6 +91,14 @@ class DeviceDecoder:
         stays below the margin."""
         N.check(N.lib().qsp_set_first_pass_margin(self.handle, float(margin0), float(margin_per_norm)))
 
+    def check_guards(self) -> int:
+        """Debug (QSP_GUARD=1 in the environment): number of workspace buffers whose canary bands were overwritten
+        since they were allocated, -1 if none is guarded; raises with the buffer names if any was."""
+        n = N.lib().qsp_check_guards(self.handle)
+        if n > 0:
+            raise N.NativeError(N.lib().qsp_last_error().decode())
+        return n
+
     def decode_sdf(self, codes, pts, mode: str = "tensor") -> np.ndarray:
         """codes (C,64) or (64,), pts (n,3) host arrays -> (C,n) or (n,) float32  (loss_utils.py:51-79).
         mode: "tensor" (fp16-pair tensor-core kernel), "fast" (single-pass fp16), "fp32" (CUDA cores)."""
