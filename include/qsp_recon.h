@@ -136,6 +136,16 @@ int qsp_get_iteration(qsp_decoder* dec, int32_t iteration, int32_t b, float* H, 
  * returns the number of candidate rows (samples re-evaluated by the fp32-equivalent kernel).    */
 int qsp_get_band_indices(qsp_decoder* dec, int32_t iteration, int32_t b, int32_t* ray,
                          int32_t* sample, int32_t cap);
+/* Loss terms of object b at a recorded `iteration`, as the reference's loss functions return them:
+ * term 0 = reconstruct/loss.py:22-43 compute_sdf_loss (one row per surface point), term 1 = loss.py:46-152
+ * compute_render_loss (one row per kept band point, (ray, sample) ascending); a row is 72 floats
+ * [J_pose(7) | J_code(64) | residual] (raw residual, before the Huber weight).  term 2 = loss.py:155-178
+ * compute_rotation_loss_sim3: one row of 8 floats [J(7) | res].  Returns the row count (cap < 0: count only;
+ * else at most cap rows are written to the host buffer `out`).                                                  */
+int qsp_get_loss_rows(qsp_decoder* dec, int32_t iteration, int32_t b, int32_t term, float* out, int32_t cap);
+/* reconstruct/loss.py:155-178 compute_rotation_loss_sim3 of one pose, without a decoder: t_obj_cam (16, host)
+ * -> out8 = [J(7) | res] (host).                                                                                */
+int qsp_rotation_prior(int32_t device, const float* t_obj_cam, float* out8);
 
 /* --- isosurface extraction: replaces reconstruct/utils.py:120-141 convert_sdf_voxels_to_mesh ------- */
 /* sdf (D,D,D) row-major (the grid decode of qsp_decode_sdf over create_voxel_grid(D));           */

@@ -69,6 +69,10 @@ struct IterDebug {
   std::vector<int> counts;             // (B,6)
   std::vector<int> band_off, row_ray, row_samp;   // candidate rows (ray-major)
   std::vector<float> row_fac;                     // de_ds of the row; 0 = not a kept band point
+  int M = 0;                                      // surface rows of the batch
+  std::vector<int> pts_off;                       // (B+1)
+  std::vector<float> rows;                        // (M + P, 72): [J_pose | J_code | residual] (k_export_rows)
+  std::vector<float> rot;                         // (B, 4): J_rot[3:6], res_rot of the iteration's pose
 };
 
 struct qsp_decoder {
@@ -854,6 +858,25 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
         CK(cudaMemcpy(g.row_samp.data(), row_samp + M, (size_t)P * 4, cudaMemcpyDeviceToHost));
         CK(cudaMemcpy(g.row_fac.data(), row_fac + M, (size_t)P * 4, cudaMemcpyDeviceToHost));
       }
+      g.M = M;
+      g.pts_off.assign(pts_off, pts_off + B + 1);
+      g.rot.resize((size_t)B * 4);
+      for (int o = 0; o < B; ++o) {
+        for (int c = 0; c < 3; ++c) g.rot[o * 4 + c] = hs[o].J_rot[c];
+        g.rot[o * 4 + 3] = hs[o].res_rot;
+      }
+      const int nrows = M + P;
+      g.rows.resize((size_t)nrows * 72);
+      if (nrows > 0) {
+        float* d_rows = nullptr;
+        CK(cudaMalloc(&d_rows, g.rows.size() * 4));
+        k_export_rows<<<(nrows + 127) / 128, 128, 0, st>>>(nrows, M, jp_pts, g_sdf, g_jac, row_fac, row_res, d_rows);
+        LAUNCHED();
+        cudaError_t e = cudaMemcpyAsync(g.rows.data(), d_rows, g.rows.size() * 4, cudaMemcpyDeviceToHost, st);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+        cudaFree(d_rows);
+        CK(e);
+      }
       d->dbg.push_back(std::move(g));
     }
   }
@@ -916,6 +939,61 @@ extern "C" int qsp_get_band_indices(qsp_decoder* d, int32_t it, int32_t b, int32
     ++n;
   }
   return n;
+}
+
+// Loss terms of a recorded iteration as the reference's loss functions return them (reconstruct/loss.py:22-43
+// compute_sdf_loss, :46-152 compute_render_loss, :155-178 compute_rotation_loss_sim3).  term 0: the object's surface
+// rows, term 1: its kept band rows in (ray, sample) order - 72 floats per row [J_pose(7) | J_code(64) | residual];
+// term 2: one row of 8 floats [J_rot(7) | res_rot].  cap < 0 returns the row count; else up to cap rows are written
+// and the count is returned.
+extern "C" int qsp_get_loss_rows(qsp_decoder* d, int32_t it, int32_t b, int32_t term, float* out, int32_t cap) {
+  if (!d || it < 0 || it >= (int)d->dbg.size()) { g_err = "no such recorded iteration"; return QSP_ERR_INVALID; }
+  const IterDebug& g = d->dbg[it];
+  if (b < 0 || b + 1 >= (int)g.pts_off.size() || b + 1 >= (int)d->h_rays_off.size()) { g_err = "no such object"; return QSP_ERR_INVALID; }
+  if (term == 2) {
+    if (cap < 0) return 1;
+    if (cap >= 1 && out) {
+      for (int c = 0; c < 7; ++c) out[c] = 0.f;
+      for (int c = 0; c < 3; ++c) out[3 + c] = g.rot[b * 4 + c];
+      out[7] = g.rot[b * 4 + 3];
+    }
+    return 1;
+  }
+  if (term == 0) {
+    const int lo = g.pts_off[b], n = g.pts_off[b + 1] - lo;
+    if (cap < 0) return n;
+    const int m = std::min(n, (int)cap);
+    if (m > 0 && out) memcpy(out, g.rows.data() + (size_t)lo * 72, (size_t)m * 72 * 4);
+    return n;
+  }
+  if (term != 1) { g_err = "term must be 0, 1 or 2"; return QSP_ERR_INVALID; }
+  const int r0 = d->h_rays_off[b], r1 = d->h_rays_off[b + 1];
+  const int lo = g.band_off[r0], hi = std::min<int>(g.band_off[r1], (int)g.row_ray.size());
+  int n = 0;
+  for (int i = lo; i < hi; ++i) {
+    if (g.row_fac[i] == 0.f) continue;
+    if (cap >= 0 && n < cap && out) memcpy(out + (size_t)n * 72, g.rows.data() + (size_t)(g.M + i) * 72, 72 * 4);
+    ++n;
+  }
+  return n;
+}
+
+// compute_rotation_loss_sim3 (reconstruct/loss.py:155-178) of one object pose: t_obj_cam (16 floats, camera -> object
+// Sim(3), host memory) -> out8 = [J (7) | res] (host memory).  Needs no decoder.
+extern "C" int qsp_rotation_prior(int32_t device, const float* t_obj_cam, float* out8) {
+  if (!t_obj_cam || !out8) { g_err = "null argument"; return QSP_ERR_INVALID; }
+  CK(cudaSetDevice(device));
+  float* dbuf = nullptr;
+  CK(cudaMalloc(&dbuf, 24 * sizeof(float)));
+  cudaError_t e = cudaMemcpy(dbuf, t_obj_cam, 16 * sizeof(float), cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    k_rotation_prior<<<1, 32>>>(dbuf, dbuf + 16);
+    LAUNCHED();
+    e = cudaMemcpy(out8, dbuf + 16, 8 * sizeof(float), cudaMemcpyDeviceToHost);
+  }
+  cudaFree(dbuf);
+  CK(e);
+  return QSP_OK;
 }
 
 // ------------------------------------------------------------------------------------------------

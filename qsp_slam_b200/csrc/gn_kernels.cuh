@@ -74,6 +74,26 @@ __global__ void k_init_state(ObjState* st, const float* __restrict__ t_cam_obj,
   s.n_inball = s.n_band = s.n_keep = 0;
 }
 
+// rotation prior of a pose (loss.py:155-178): res = 1 - (R_co e_y).n_g = 1 + R_co[1][1] with R_co = T_co[:3,:3] / scale;
+// J[3:6] = (R_oc n_g) x e_y, zero (and res = 0) when res < 1e-7
+__device__ inline void rotation_prior_dev(const float* T_co, float scale, float* J_rot, float* res_rot) {
+  double rc[9], ro[9], dd;
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < 3; ++c) rc[r * 3 + c] = (double)__fdiv_rn(T_co[r * 4 + c], scale);
+  float res = __fadd_rn(1.0f, (float)rc[4]);
+  if (res < 1e-7f) {
+    J_rot[0] = J_rot[1] = J_rot[2] = 0.f;
+    *res_rot = 0.f;
+  } else {
+    inv3_d(rc, ro, &dd);                              // R_oc
+    // (R_oc n_g) x e_y with n_g = (0,-1,0): v = -R_oc[:,1]; v x e_y = (-v_z, 0, v_x)
+    J_rot[0] = (float)ro[7];
+    J_rot[1] = 0.f;
+    J_rot[2] = (float)(-ro[1]);
+    *res_rot = res;
+  }
+}
+
 // depth range, background depth and rotation prior of the current pose (optimizer.py:144-153,
 // loss.py:155-178)
 __global__ void k_prep(ObjState* st, int B, int S, int* phase_cnt, float th, float margin0, float margin_per_norm) {
@@ -97,22 +117,23 @@ __global__ void k_prep(ObjState* st, int B, int S, int* phase_cnt, float th, flo
   float zz = 0.f;
   for (int c = 0; c < QSP_CODE; ++c) zz = fmaf(s.code[c], s.code[c], zz);
   s.cand_lim = th + margin0 + margin_per_norm * sqrtf(zz);
-  // rotation prior: res = 1 - (R_co e_y).n_g = 1 + R_co[1][1]
-  double rc[9], ro[9], dd;
-  for (int r = 0; r < 3; ++r)
-    for (int c = 0; c < 3; ++c) rc[r * 3 + c] = (double)__fdiv_rn(s.T_co[r * 4 + c], scale);
-  float res = __fadd_rn(1.0f, (float)rc[4]);
-  if (res < 1e-7f) {
-    s.J_rot[0] = s.J_rot[1] = s.J_rot[2] = 0.f;
-    s.res_rot = 0.f;
-  } else {
-    inv3_d(rc, ro, &dd);                              // R_oc
-    // (R_oc n_g) x e_y with n_g = (0,-1,0): v = -R_oc[:,1]; v x e_y = (-v_z, 0, v_x)
-    s.J_rot[0] = (float)ro[7];
-    s.J_rot[1] = 0.f;
-    s.J_rot[2] = (float)(-ro[1]);
-    s.res_rot = res;
-  }
+  rotation_prior_dev(s.T_co, scale, s.J_rot, &s.res_rot);
+}
+
+// compute_rotation_loss_sim3 (loss.py:155-178) of one pose on its own: out = [J (7) | res]
+__global__ void k_rotation_prior(const float* __restrict__ t_obj_cam, float* __restrict__ out) {
+  if (threadIdx.x || blockIdx.x) return;
+  float T_co[16], J[3], res;
+  const float det = inv_affine(t_obj_cam, T_co);      // det(T_oc[:3,:3]) = 1 / det(T_co[:3,:3])
+  (void)det;
+  const float* C = T_co;
+  double dco = (double)C[0] * ((double)C[5] * C[10] - (double)C[6] * C[9]) -
+               (double)C[1] * ((double)C[4] * C[10] - (double)C[6] * C[8]) +
+               (double)C[2] * ((double)C[4] * C[9] - (double)C[5] * C[8]);
+  rotation_prior_dev(T_co, cbrtf((float)dco), J, &res);
+  for (int c = 0; c < 7; ++c) out[c] = 0.f;
+  out[3] = J[0]; out[4] = J[1]; out[5] = J[2];
+  out[7] = res;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -502,6 +523,28 @@ k_accumulate(const ObjState* __restrict__ st, const int* __restrict__ pts_off,
         if (j >= i) out[i * 72 - i * (i - 1) / 2 + (j - i)] = acc[r][c];
       }
   }
+}
+
+// Debug export of the loss terms as the reference returns them (loss.py:36-43, 143-152): per Jacobian row
+// [J_pose(7) | J_code(64) | raw residual], the same arithmetic as the staging of k_accumulate (no Huber weight).
+// Rows < M are surface points (factor 1, residual = SDF), the others candidate rows (factor de_ds, 0 = not kept).
+__global__ void k_export_rows(int n_rows, int M, const float* __restrict__ jp_pts, const float* __restrict__ g_sdf,
+                              const float* __restrict__ g_jac, const float* __restrict__ row_fac,
+                              const float* __restrict__ row_res, float* __restrict__ out) {
+  int row = blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= n_rows) return;
+  const float fac = row < M ? 1.f : row_fac[row];
+  const float* g = g_jac + (size_t)row * QSP_JSTRIDE;
+  float* o = out + (size_t)row * 72;
+  const float gx = fac * g[64], gy = fac * g[65], gz = fac * g[66];
+  const float x = jp_pts[row * 3], y = jp_pts[row * 3 + 1], z = jp_pts[row * 3 + 2];
+  o[0] = gx; o[1] = gy; o[2] = gz;
+  o[3] = gy * (-z) + gz * y;
+  o[4] = gx * z + gz * (-x);
+  o[5] = gx * (-y) + gy * x;
+  o[6] = gx * x + gy * y + gz * z;
+  for (int c = 0; c < 64; ++c) o[7 + c] = fac * g[c];
+  o[71] = row < M ? g_sdf[row] : row_res[row];
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -477,3 +477,57 @@ def test_first_pass_margin_only_changes_the_amount_of_exact_work(golden, decoder
     assert np.abs(o1.t_cam_obj - o0.t_cam_obj).max() < 1e-5 and np.abs(o1.code - o0.code).max() < 1e-5
     with pytest.raises(Exception):
         DeviceDecoder(decoder_state, 0).set_first_pass_margin(-1.0, 0.0)
+
+
+@pytest.mark.parametrize("precision", ["tensor", "fp32"])
+@pytest.mark.parametrize("name", ["kitti0", "kitti1", "redwood0", "redwood1"])
+def test_loss_terms_vs_reference(golden, dev, name, precision):
+    """reconstruct.loss under the reference's names (loss.py:22-178) against the unmodified reference's own rows:
+    surface term, render term (identical kept band points, in order), rotation prior.  Same checks and row
+    tolerances as the oracle's test (tests/test_oracle_golden.py::test_loss_terms); the tensor mode holds the SDF
+    residual to 2e-5 (fp32 mode 5e-6) and its Jacobian rows to 1e-3 relative (north_star)."""
+    from qsp_slam_b200.reconstruct import loss as L
+    p = name + "_"
+    t_oc = np.linalg.inv(golden[p + "t_cam_obj"].astype(np.float64)).astype(np.float32)
+    z = golden[p + "code0"]
+    dev.set_precision(precision)
+    try:
+        jp, jc, rs = L.compute_sdf_loss(dev, golden[p + "pts"], t_oc, z)
+        M = golden[p + "pts"].shape[0]
+        assert jp.shape == (M, 1, 7) and jc.shape == (M, 1, 64) and rs.shape == (M, 1, 1)
+        tol_res, tol_rows = (5e-6, 3e-5) if precision == "fp32" else (2e-5, 1e-3)
+        assert np.abs(rs.reshape(-1) - golden[p + "sdf_res"]).max() < tol_res
+        assert rows_close(jp[:, 0], golden[p + "sdf_Jpose"], tol_rows)
+        assert rows_close(jc[:, 0], golden[p + "sdf_Jcode"], tol_rows)
+        # render term: depth_obs as optimizer.py:153 builds it
+        t_co = np.linalg.inv(t_oc.astype(np.float64))
+        d_max = t_co[2, 3] + np.cbrt(np.linalg.det(t_co[:3, :3]))
+        rays, K = golden[p + "rays"], golden[p + "depth"].shape[0]
+        dobs = np.concatenate([golden[p + "depth"], np.full(rays.shape[0] - K, 1.1 * d_max, np.float32)]).astype(np.float32)
+        out = L.compute_render_loss(dev, rays, dobs, t_oc, golden[p + "sampled"], z, th=0.01)
+        assert out is not None
+        jp, jc, rd = out
+        P = golden[p + "ren_res"].shape[0]
+        assert jp.shape == (P, 1, 7) and jc.shape == (P, 1, 64) and rd.shape == (P, 1, 1)    # identical band-point set
+        # the depth residual moves by (d_max - d_min) / (2 th) = 100..200 times the SDF error of a band sample: an SDF
+        # that differs from the reference's by fp32 rounding (1e-6, another summation order) moves it by 2e-5
+        assert np.abs(rd.reshape(-1) - golden[p + "ren_res"]).max() < 5e-5
+        # the rows carry the factor de_ds, which has the same sensitivity to the SDF of the ray's band samples
+        tol_rows = 3e-4 if precision == "fp32" else 1e-3
+        assert rows_close(jp[:, 0], golden[p + "ren_Jpose"], tol_rows, 0.02)
+        assert rows_close(jc[:, 0], golden[p + "ren_Jcode"], tol_rows, 0.02)
+        with pytest.raises(ValueError):
+            L.compute_render_loss(dev, rays, dobs, t_oc, golden[p + "sampled"] * 1.01, z, th=0.01)
+        # fewer than 10 in-ball samples -> None (loss.py:73-74)
+        far = rays.copy(); far[:, 0] += 5.0
+        assert L.compute_render_loss(dev, far, dobs, t_oc, golden[p + "sampled"], z, th=0.01) is None
+    finally:
+        dev.set_precision("tensor")
+    J, res = L.compute_rotation_loss_sim3(t_oc)
+    assert J.shape == (7,)
+    assert abs(res - float(golden[p + "rot_res"])) < 2e-7
+    if res > 3e-7 and float(golden[p + "rot_res"]) > 3e-7:
+        assert np.abs(J - golden[p + "rot_J"]).max() < 1e-5
+    # torch in -> torch out
+    jp_t, jc_t, rs_t = L.compute_sdf_loss(dev, torch.from_numpy(golden[p + "pts"]), torch.from_numpy(t_oc), torch.from_numpy(z))
+    assert isinstance(rs_t, torch.Tensor) and rs_t.shape == (golden[p + "pts"].shape[0], 1, 1)
