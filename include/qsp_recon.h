@@ -147,6 +147,17 @@ int qsp_get_loss_rows(qsp_decoder* dec, int32_t iteration, int32_t b, int32_t te
  * -> out8 = [J(7) | res] (host).                                                                                */
 int qsp_rotation_prior(int32_t device, const float* t_obj_cam, float* out8);
 
+/* --- the small helpers of reconstruct/loss_utils.py on their own (host arrays in and out, no decoder); the same
+ * device functions the Gauss-Newton kernels use ------------------------------------------------------------ */
+/* loss_utils.py:188-233 exp_sim3 (se3 = 0, x (n,7)) / :129-163 exp_se3 (se3 = 1, x (n,6)) -> out (n,16)      */
+int qsp_exp_map(int32_t device, const float* x, int32_t n, int32_t se3, float* out);
+/* loss_utils.py:250-265 get_robust_res + :236-247 huber_norm_weights: res (n) -> robust (n), w (n), loss (1)   */
+int qsp_robust_res(int32_t device, const float* res, int32_t n, float b, float* robust, float* w, float* loss);
+/* loss_utils.py:40-48 sdf_to_occupancy                                                                         */
+int qsp_sdf_to_occupancy(int32_t device, const float* sdf, int64_t n, float th, float* out);
+/* loss_utils.py:166-185 get_points_to_pose_jacobian_sim3 (se3 = 0, out (n,3,7)) / :107-126 _se3 (out (n,3,6))  */
+int qsp_point_pose_jacobian(int32_t device, const float* pts, int32_t n, int32_t se3, float* out);
+
 /* --- isosurface extraction: replaces reconstruct/utils.py:120-141 convert_sdf_voxels_to_mesh ------- */
 /* sdf (D,D,D) row-major (the grid decode of qsp_decode_sdf over create_voxel_grid(D));           */
 /* vertices (V,3) float32 = array index * spacing + origin, faces (F,3) int32.  Marching           */

@@ -997,6 +997,90 @@ extern "C" int qsp_rotation_prior(int32_t device, const float* t_obj_cam, float*
 }
 
 // ------------------------------------------------------------------------------------------------
+// helpers of reconstruct/loss_utils.py on their own: host arrays in, host arrays out, no decoder
+// ------------------------------------------------------------------------------------------------
+namespace {
+struct Scratch {                       // device scratch of one helper call
+  std::vector<void*> p;
+  ~Scratch() { for (void* q : p) cudaFree(q); }
+  float* get(size_t n_floats) {
+    void* q = nullptr;
+    if (cudaMalloc(&q, std::max<size_t>(n_floats, 1) * sizeof(float)) != cudaSuccess) return nullptr;
+    p.push_back(q);
+    return static_cast<float*>(q);
+  }
+};
+}  // namespace
+#define UTIL_BEGIN(device)                                     \
+  CK(cudaSetDevice(device));                                   \
+  Scratch scratch
+#define UTIL_ALLOC(ptr, n)                                     \
+  float* ptr = scratch.get(n);                                 \
+  if (!ptr) { g_err = "cudaMalloc failed"; return QSP_ERR_ALLOC; }
+
+// loss_utils.py:188-233 exp_sim3 (se3 = 0: x is (n,7)) / :129-163 exp_se3 (se3 = 1: x is (n,6)) -> out (n,16)
+extern "C" int qsp_exp_map(int32_t device, const float* x, int32_t n, int32_t se3, float* out) {
+  if (n < 0 || (n > 0 && (!x || !out))) { g_err = "bad argument"; return QSP_ERR_INVALID; }
+  if (n == 0) return QSP_OK;
+  UTIL_BEGIN(device);
+  const int w = se3 ? 6 : 7;
+  UTIL_ALLOC(dx, (size_t)n * w);
+  UTIL_ALLOC(dout, (size_t)n * 16);
+  CK(cudaMemcpy(dx, x, (size_t)n * w * 4, cudaMemcpyHostToDevice));
+  k_util_exp<<<(n + 63) / 64, 64>>>(dx, n, se3, dout);
+  LAUNCHED();
+  CK(cudaMemcpy(out, dout, (size_t)n * 16 * 4, cudaMemcpyDeviceToHost));
+  return QSP_OK;
+}
+
+// loss_utils.py:250-265 get_robust_res: res (n) -> robust (n), w (n), loss (1) = mean(robust^2)
+extern "C" int qsp_robust_res(int32_t device, const float* res, int32_t n, float b, float* robust, float* w, float* loss) {
+  if (n < 0 || !loss || (n > 0 && (!res || !robust || !w))) { g_err = "bad argument"; return QSP_ERR_INVALID; }
+  if (n == 0) { *loss = NAN; return QSP_OK; }              // torch.mean of an empty tensor (optimizer.py:168)
+  UTIL_BEGIN(device);
+  UTIL_ALLOC(dres, n);
+  UTIL_ALLOC(dout, (size_t)2 * n + 1);
+  CK(cudaMemcpy(dres, res, (size_t)n * 4, cudaMemcpyHostToDevice));
+  k_util_robust<<<1, 256>>>(dres, n, b, dout, dout + n, dout + 2 * (size_t)n);
+  LAUNCHED();
+  CK(cudaMemcpy(robust, dout, (size_t)n * 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(w, dout + n, (size_t)n * 4, cudaMemcpyDeviceToHost));
+  CK(cudaMemcpy(loss, dout + 2 * (size_t)n, 4, cudaMemcpyDeviceToHost));
+  return QSP_OK;
+}
+
+// loss_utils.py:40-48 sdf_to_occupancy
+extern "C" int qsp_sdf_to_occupancy(int32_t device, const float* sdf, int64_t n, float th, float* out) {
+  if (n < 0 || (n > 0 && (!sdf || !out))) { g_err = "bad argument"; return QSP_ERR_INVALID; }
+  if (n == 0) return QSP_OK;
+  UTIL_BEGIN(device);
+  UTIL_ALLOC(din, (size_t)n);
+  UTIL_ALLOC(dout, (size_t)n);
+  CK(cudaMemcpy(din, sdf, (size_t)n * 4, cudaMemcpyHostToDevice));
+  k_util_occupancy<<<(unsigned)((n + 255) / 256), 256>>>(din, (long)n, th, dout);
+  LAUNCHED();
+  CK(cudaMemcpy(out, dout, (size_t)n * 4, cudaMemcpyDeviceToHost));
+  return QSP_OK;
+}
+
+// loss_utils.py:166-185 get_points_to_pose_jacobian_sim3 (se3 = 0: out (n,3,7)) / :107-126 ..._se3 (se3 = 1: (n,3,6))
+extern "C" int qsp_point_pose_jacobian(int32_t device, const float* pts, int32_t n, int32_t se3, float* out) {
+  if (n < 0 || (n > 0 && (!pts || !out))) { g_err = "bad argument"; return QSP_ERR_INVALID; }
+  if (n == 0) return QSP_OK;
+  UTIL_BEGIN(device);
+  const int w = se3 ? 6 : 7;
+  UTIL_ALLOC(din, (size_t)n * 3);
+  UTIL_ALLOC(dout, (size_t)n * 3 * w);
+  CK(cudaMemcpy(din, pts, (size_t)n * 12, cudaMemcpyHostToDevice));
+  k_util_point_jacobian<<<(n + 127) / 128, 128>>>(din, n, se3, dout);
+  LAUNCHED();
+  CK(cudaMemcpy(out, dout, (size_t)n * 3 * w * 4, cudaMemcpyDeviceToHost));
+  return QSP_OK;
+}
+#undef UTIL_BEGIN
+#undef UTIL_ALLOC
+
+// ------------------------------------------------------------------------------------------------
 // pose-only GN (optimizer.py:47-93)
 // ------------------------------------------------------------------------------------------------
 extern "C" int qsp_estimate_pose_batch(qsp_decoder* d, int32_t num_iterations, int32_t B,

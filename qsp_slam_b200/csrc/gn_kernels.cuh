@@ -58,6 +58,11 @@ __device__ __forceinline__ bool in_ball(float x, float y, float z) {
   return sqrtf(__fadd_rn(__fadd_rn(__fmul_rn(x, x), __fmul_rn(y, y)), __fmul_rn(z, z))) < 1.0f;  // loss.py:68
 }
 
+// sdf_to_occupancy (loss_utils.py:40-48): 0.5 - clamp(s, -th, th) / (2 th)
+__device__ __forceinline__ float occupancy_dev(float s, float th) {
+  return __fsub_rn(0.5f, __fdiv_rn(fminf(fmaxf(s, -th), th), 2.f * th));
+}
+
 // ------------------------------------------------------------------------------------------------
 // state set-up
 // ------------------------------------------------------------------------------------------------
@@ -285,7 +290,6 @@ __global__ void k_render(ObjState* __restrict__ st, const float* __restrict__ ra
   bool band[GN_MAXC];
   int cnt = 0, base = ray_base[r];
   const int nev = ray_nev[r];                          // samples behind it were not decoded: T is exactly 0 there
-  const float inv2th = 2.f * th;
   // occupancy per sample; samples outside the ball keep occupancy 0 (loss.py:84-86)
 #pragma unroll
   for (int ch = 0; ch < GN_MAXC; ++ch) {
@@ -303,7 +307,7 @@ __global__ void k_render(ObjState* __restrict__ st, const float* __restrict__ ra
       if (in) {
         const int qi = cnt + __popc(m & ((1u << lane) - 1u));
         float s = qi < nev ? q_sdf[base + qi] : -1.f;
-        occ[ch] = __fsub_rn(0.5f, __fdiv_rn(fminf(fmaxf(s, -th), th), inv2th));  // loss_utils.py:46-47
+        occ[ch] = occupancy_dev(s, th);                                          // loss_utils.py:46-47
         band[ch] = (s > -th) && (s < th);                                        // loss.py:88
       }
       cnt += __popc(m);
@@ -558,7 +562,10 @@ __device__ inline void exp_sim3_dev(const float* x, float* M, bool se3) {
     for (int c = 0; c < 3; ++c)
       wh2[r * 3 + c] = wh[r * 3] * wh[c] + wh[r * 3 + 1] * wh[3 + c] + wh[r * 3 + 2] * wh[6 + c];
   float th = sqrtf(w[0] * w[0] + w[1] * w[1] + w[2] * w[2]);
-  float th2 = th * th, sn = sinf(th), cs = cosf(th), es = se3 ? 1.f : expf(s), s2 = s * s;
+  // sin, cos, exp correctly rounded (fp64 evaluation, one rounding) as the host libm of the reference gives them:
+  // (e^s - 1) / s amplifies a 1-ulp difference of e^s to 6e-6 relative in the translation for s = 0.02
+  float th2 = th * th, sn = (float)sin((double)th), cs = (float)cos((double)th);
+  float es = se3 ? 1.f : (float)exp((double)s), s2 = s * s;
   float ew[9], jm[9];
   const float eye[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
   if (th <= 1e-8f) {
@@ -804,6 +811,60 @@ k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
 }
 
 // records: t_cam_obj (16) | code (64) | is_good | loss  (optimizer.py:274-281)
+// ------------------------------------------------------------------------------------------------
+// The small helpers of reconstruct/loss_utils.py on their own (same device functions as the loop uses), for
+// callers of the reference's names and for parity tests against its outputs.
+// ------------------------------------------------------------------------------------------------
+// exp_sim3 (loss_utils.py:188-233; x has 7 entries) or exp_se3 (:129-163; 6 entries) of n vectors -> n 4x4 matrices
+__global__ void k_util_exp(const float* __restrict__ x, int n, int se3, float* __restrict__ out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float v[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f}, M[16];
+  const int w = se3 ? 6 : 7;
+  for (int c = 0; c < w; ++c) v[c] = x[i * w + c];
+  exp_sim3_dev(v, M, se3 != 0);
+  for (int c = 0; c < 16; ++c) out[i * 16 + c] = M[c];
+}
+
+// get_robust_res (loss_utils.py:250-265): robust = w * res with the Huber weight of |res|, loss = mean(robust^2).
+// One block; the sum runs in a fixed order.
+__global__ void k_util_robust(const float* __restrict__ res, int n, float b, float* __restrict__ robust,
+                              float* __restrict__ w, float* __restrict__ loss) {
+  __shared__ float red[256];
+  float acc = 0.f;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) {
+    const float r = res[i], wi = huber_weight(r, b), rr = wi * r;
+    robust[i] = rr;
+    w[i] = wi;
+    acc += rr * rr;
+  }
+  red[threadIdx.x] = acc;
+  __syncthreads();
+  for (int d = blockDim.x / 2; d > 0; d >>= 1) {
+    if (threadIdx.x < d) red[threadIdx.x] += red[threadIdx.x + d];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *loss = red[0] / (float)n;
+}
+
+__global__ void k_util_occupancy(const float* __restrict__ sdf, long n, float th, float* __restrict__ out) {
+  long i = (long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = occupancy_dev(sdf[i], th);
+}
+
+// get_points_to_pose_jacobian_sim3 (loss_utils.py:166-185): [I | -[x]x | x] (n,3,7);
+// get_points_to_pose_jacobian_se3 (:107-126): [I | -[x]x] (n,3,6).  -[x]x = [[0,z,-y],[-z,0,x],[y,-x,0]]
+__global__ void k_util_point_jacobian(const float* __restrict__ pts, int n, int se3, float* __restrict__ out) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const float x = pts[i * 3], y = pts[i * 3 + 1], z = pts[i * 3 + 2];
+  const int w = se3 ? 6 : 7;
+  float* o = out + (size_t)i * 3 * w;
+  const float rows[3][7] = {{1.f, 0.f, 0.f, 0.f, z, -y, x}, {0.f, 1.f, 0.f, -z, 0.f, x, y}, {0.f, 0.f, 1.f, y, -x, 0.f, z}};
+  for (int r = 0; r < 3; ++r)
+    for (int c = 0; c < w; ++c) o[r * w + c] = rows[r][c];
+}
+
 __global__ void k_finalize(const ObjState* __restrict__ st, int B, float* __restrict__ records) {
   pdl_prologue();
   int o = blockIdx.x * blockDim.x + threadIdx.x;

@@ -531,3 +531,35 @@ def test_loss_terms_vs_reference(golden, dev, name, precision):
     # torch in -> torch out
     jp_t, jc_t, rs_t = L.compute_sdf_loss(dev, torch.from_numpy(golden[p + "pts"]), torch.from_numpy(t_oc), torch.from_numpy(z))
     assert isinstance(rs_t, torch.Tensor) and rs_t.shape == (golden[p + "pts"].shape[0], 1, 1)
+
+
+def test_loss_utils_helpers_vs_reference(golden, orc):
+    """The small helpers of loss_utils.py under the reference's names - the device functions the GN kernels use,
+    run on their own (qsp_exp_map, qsp_robust_res, qsp_sdf_to_occupancy, qsp_point_pose_jacobian) - against the
+    unmodified reference's outputs (exp maps incl. the zero-rotation, zero-scale and small-angle branches; Huber
+    incl. zero residuals) and, where the fixtures hold none, against the oracle (bit-exact: no rounding involved
+    beyond one division)."""
+    from qsp_slam_b200.reconstruct import loss_utils as LU
+    G, _ = orc
+    for v, e7, e6 in zip(golden["exp_in"], golden["exp_sim3"], golden["exp_se3"]):
+        assert np.abs(LU.exp_sim3(v) - e7).max() < 1e-6
+        assert np.abs(LU.exp_se3(v[:6]) - e6).max() < 1e-6
+    rr, loss, w = LU.get_robust_res(golden["rob_in"], 0.025)
+    assert rr.shape == (200, 1, 1) and w.shape == (200, 1, 1)
+    assert np.abs(rr.reshape(-1) - golden["rob_res"]).max() < 1e-7
+    assert np.abs(w.reshape(-1) - golden["rob_w"]).max() < 1e-6
+    assert abs(loss - float(golden["rob_loss"])) < 1e-6 * float(golden["rob_loss"])
+    w2 = LU.huber_norm_weights(np.abs(golden["rob_in"]), 0.025)
+    assert np.abs(w2 - golden["rob_w"]).max() < 1e-6
+    rng = np.random.default_rng(3)
+    s = (rng.standard_normal(1000) * 0.02).astype(np.float32)
+    s[:4] = [0.01, -0.01, 0.0, 0.3]
+    np.testing.assert_array_equal(LU.sdf_to_occupancy(s, 0.01), G.sdf_to_occupancy(torch.from_numpy(s), 0.01).numpy())
+    p = rng.standard_normal((37, 3)).astype(np.float32)
+    J7 = LU.get_points_to_pose_jacobian_sim3(p)
+    np.testing.assert_array_equal(J7, G.points_to_pose_jacobian_sim3(torch.from_numpy(p)).numpy().reshape(37, 3, 7))
+    np.testing.assert_array_equal(LU.get_points_to_pose_jacobian_se3(p), J7[:, :, :6])
+    # torch in -> torch out; empty input
+    assert isinstance(LU.exp_sim3(torch.from_numpy(golden["exp_in"][0])), torch.Tensor)
+    assert LU.sdf_to_occupancy(np.zeros(0, np.float32), 0.01).shape == (0,)
+    assert np.isnan(LU.get_robust_res(np.zeros(0, np.float32), 0.02)[1])
