@@ -91,6 +91,35 @@ class DeviceDecoder:
         stays below the margin."""
         N.check(N.lib().qsp_set_first_pass_margin(self.handle, float(margin0), float(margin_per_norm)))
 
+    def calibrate_first_pass_margin(self, code_norms=(0.0, 0.4, 0.8, 1.6, 2.4), n_points: int = 262144, codes_per_norm: int = 4,
+                                    safety: float = 1.5, seed: int = 0, allow_lower: bool = False) -> dict:
+        """Measures the error of the fp16 first pass against the fp32-equivalent kernel on THIS decoder's weights and
+        sets the margin from it (a trained decoder may have larger activations than the random-init decoders the
+        defaults were measured on, ``scripts/fast_error_tail.py``).  For every code norm in ``code_norms``,
+        ``codes_per_norm`` random codes of that norm are decoded at ``n_points`` uniform points of the unit ball in
+        both modes; margin0 = safety * max error at norm 0, margin_per_norm = safety * the largest slope
+        (err(norm) - err(0)) / norm.  The margins are never set below the defaults unless ``allow_lower``.  Returns
+        the measured maxima and the margins in force.  Runs entirely on the device (two decoder launches per norm)."""
+        rng = np.random.default_rng(seed)
+        x = rng.standard_normal((n_points, 3))
+        x = (x / np.linalg.norm(x, axis=1, keepdims=True) * rng.random((n_points, 1)) ** (1.0 / 3.0)).astype(np.float32)
+        err = {}
+        for nz in code_norms:
+            z = rng.standard_normal((codes_per_norm, N.CODE_LEN))
+            z = (z / np.linalg.norm(z, axis=1, keepdims=True) * nz).astype(np.float32)
+            if nz == 0.0:
+                z = z[:1]
+            fast = self.decode_sdf(z, x, mode="fast")
+            exact = self.decode_sdf(z, x, mode="tensor")
+            err[float(nz)] = float(np.abs(fast - exact).max())
+        e0 = err.get(0.0, min(err.values()))
+        slope = max([0.0] + [(e - e0) / nz for nz, e in err.items() if nz > 0.0])
+        m0, m1 = safety * e0, safety * slope
+        if not allow_lower:
+            m0, m1 = max(m0, 0.0045), max(m1, 0.004)
+        self.set_first_pass_margin(m0, m1)
+        return dict(max_error_by_code_norm=err, margin0=m0, margin_per_norm=m1)
+
     def check_guards(self) -> int:
         """Debug (QSP_GUARD=1 in the environment): number of workspace buffers whose canary bands were overwritten
         since they were allocated, -1 if none is guarded; raises with the buffer names if any was."""

@@ -563,3 +563,26 @@ def test_loss_utils_helpers_vs_reference(golden, orc):
     assert isinstance(LU.exp_sim3(torch.from_numpy(golden["exp_in"][0])), torch.Tensor)
     assert LU.sdf_to_occupancy(np.zeros(0, np.float32), 0.01).shape == (0,)
     assert np.isnan(LU.get_robust_res(np.zeros(0, np.float32), 0.02)[1])
+
+
+def test_first_pass_margin_calibration(decoder_state):
+    """DeviceDecoder.calibrate_first_pass_margin measures the fp16 first-pass error on the decoder's own weights.
+    Calibrated random-init decoder: errors below the defaults' budget, defaults stay.  The same decoder with a
+    3x larger output layer (3x larger pre-tanh values near the surface): larger errors, larger margin."""
+    from qsp_slam_b200.decoder import DeviceDecoder
+    d = DeviceDecoder(decoder_state, 0)
+    r = d.calibrate_first_pass_margin(n_points=65536)
+    e = r["max_error_by_code_norm"]
+    assert 0 < e[0.0] < 0.0045 / 1.5 and e[2.4] > e[0.0]
+    assert all(e[n] < (0.0045 + 0.004 * n) for n in e)                    # the defaults cover every measured norm
+    assert r["margin0"] == 0.0045 and r["margin_per_norm"] == 0.004
+    low = d.calibrate_first_pass_margin(n_points=65536, allow_lower=True)
+    assert low["margin0"] == pytest.approx(1.5 * e[0.0]) and low["margin0"] < 0.0045
+    d.close()
+    hot = {k: np.array(v, copy=True) for k, v in decoder_state.items()}
+    hot["lin8.weight"] = hot["lin8.weight"] * 3.0
+    h = DeviceDecoder(hot, 0)
+    rh = h.calibrate_first_pass_margin(n_points=65536)
+    assert rh["max_error_by_code_norm"][0.0] > 1.5 * e[0.0]
+    assert rh["margin0"] > 0.0045
+    h.close()
