@@ -104,3 +104,52 @@ def test_extract_map_objects_driver(tmp_path):
         assert v.shape == one.vertices.shape and f.shape == one.faces.shape
         np.testing.assert_allclose(v, one.vertices, atol=1e-4)
         assert f.size == 0 or (f.min() >= 0 and f.max() < v.shape[0])
+
+
+def test_multi_class_settings_yaml(tmp_path):
+    """extract_map_objects_multi.py:28-33: OpenCV FileStorage YAML, first line skipped."""
+    from qsp_slam_b200 import extract_map_objects_multi as M
+    y = tmp_path / "settings.yaml"
+    y.write_text("%YAML:1.0\nYoloClasses: [56, 62]\nDecoderPaths: ['weights/chairs_64', 'weights/monitors_64']\nCamera.fx: 535.4\n")
+    d = M.read_yaml_file(str(y))
+    assert d["YoloClasses"] == [56, 62] and d["DecoderPaths"][1] == "weights/monitors_64"
+    a = M.config_parser().parse_args(["-y", str(y), "-m", "map"])
+    assert a.voxels_dim == 128 and a.map_dir == "map"
+
+
+@pytest.mark.gpu
+def test_extract_map_objects_multi_driver(tmp_path):
+    """Two classes with two different decoders (experiment directories in the reference's checkpoint format): every
+    object is meshed by the decoder of its class."""
+    import json
+    import torch
+    from qsp_slam_b200 import synth, extract_map_objects_multi as M
+    from qsp_slam_b200.deep_sdf.workspace import config_decoder
+    from qsp_slam_b200.reconstruct.optimizer import MeshExtractor
+    paths = []
+    for cls, seed in ((56, 0), (62, 1)):
+        d = tmp_path / f"dec{cls}"
+        (d / "ModelParameters").mkdir(parents=True)
+        (d / "specs.json").write_text(json.dumps({"CodeLength": 64, "NetworkSpecs": {"dims": [512] * 8, "latent_in": [4],
+                                                  "weight_norm": True, "xyz_in_all": False}}))
+        st = {"module." + k: torch.from_numpy(np.asarray(v)) for k, v in synth.make_decoder_state(seed).items()}
+        torch.save({"model_state_dict": st, "epoch": 1}, str(d / "ModelParameters" / "latest.pth"))
+        paths.append(str(d))
+    (tmp_path / "settings.yaml").write_text("%YAML:1.0\nYoloClasses: [56, 62]\nDecoderPaths: ['" + paths[0] + "', '" + paths[1] + "']\n")
+    objs = _objects(4, seed=9)
+    for i, o in enumerate(objs):
+        o["code"] = (o["code"] * 0.3).astype(np.float32)
+        o["label"] = 56 if i % 2 == 0 else 62
+    map_dir = tmp_path / "map"
+    map_dir.mkdir()
+    map_io.write_map_objects(str(map_dir / "MapObjects.txt"), objs)
+    done = M.main(["-y", str(tmp_path / "settings.yaml"), "-m", str(map_dir), "-n", "24"])
+    assert sorted(done) == sorted(o["id"] for o in objs)
+    ex = {56: MeshExtractor(config_decoder(paths[0]), 64, 24), 62: MeshExtractor(config_decoder(paths[1]), 64, 24)}
+    for o in map_io.read_map_objects(str(map_dir / "MapObjects.txt")):
+        v, f = map_io.read_ply(os.path.join(map_dir, "objects", "%d.ply" % o["id"]))
+        own = ex[o["label"]].extract_mesh_from_code(o["code"])
+        other = ex[56 if o["label"] == 62 else 62].extract_mesh_from_code(o["code"])
+        assert v.shape == own.vertices.shape
+        np.testing.assert_allclose(v, own.vertices, atol=1e-4)
+        assert v.shape != other.vertices.shape or not np.allclose(v, other.vertices, atol=1e-4)
