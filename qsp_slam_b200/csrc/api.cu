@@ -90,7 +90,7 @@ struct qsp_decoder {
   Buf grid_pts, grid_sdf, grid_need, grid_list, grid_cnt, grid_code;   // qsp_extract_mesh
   int grid_D = 0;
   Buf jp_pts, jp_code, g_sdf, g_jac, row_fac, row_res, row_ray, row_samp, row_active, m_active;
-  Buf partials, dbgH, dbgb, dbgdx;
+  Buf partials, reduced, dbgH, dbgb, dbgdx;
   Buf dec_pts, dec_codes, dec_out, dec_jac;
   bool debug = false;
   std::vector<IterDebug> dbg;
@@ -105,6 +105,7 @@ struct qsp_decoder {
   int t3_grid = 148;
   float margin0 = QSP_FAST_MARGIN0, margin1 = QSP_FAST_MARGIN_PER_NORM;   // first-pass margin = margin0 + margin1 * |code|
   bool phases = true;                              // first pass front to back in phases of 32 samples per ray
+  int pre_reduce = -1;                             // QSP_REDUCE=0/1: k_reduce_partials before k_solve (default: when >= 8 chunks)
   bool timeline = false;                           // QSP_TIMELINE=1: CUDA-event time of every launch group of one GN iteration
 };
 
@@ -361,6 +362,7 @@ extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_
   CK(cudaFuncSetAttribute(k_decoder_ffma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FF_SMEM_BYTES));
   if (const char* e = getenv("QSP_PHASES")) d->phases = atoi(e) != 0;
   if (const char* e = getenv("QSP_TIMELINE")) d->timeline = atoi(e) != 0;
+  if (const char* e = getenv("QSP_REDUCE")) d->pre_reduce = atoi(e) != 0;
   if (const char* dbg_env = getenv("QSP_TC_DEBUG")) {
     int v = atoi(dbg_env);
     CK(cudaMemcpyToSymbol(g_tc_dbg, &v, sizeof(int)));
@@ -379,7 +381,7 @@ static std::vector<std::pair<const char*, Buf*>> all_bufs(qsp_decoder* d) {
           NB(band_cnt), NB(band_base), NB(q_pts), NB(q_code), NB(q_samp), NB(cand_q), NB(q_sdf), NB(slot), NB(ray_res),
           NB(ray_nev), NB(ph_list), NB(ph_code), NB(grid_pts), NB(grid_sdf), NB(grid_need), NB(grid_list), NB(grid_cnt),
           NB(grid_code), NB(jp_pts), NB(jp_code), NB(g_sdf), NB(g_jac), NB(row_fac), NB(row_res), NB(row_ray),
-          NB(row_samp), NB(row_active), NB(m_active), NB(partials), NB(dbgH), NB(dbgb), NB(dbgdx), NB(dec_pts),
+          NB(row_samp), NB(row_active), NB(m_active), NB(partials), NB(reduced), NB(dbgH), NB(dbgb), NB(dbgdx), NB(dec_pts),
           NB(dec_codes), NB(dec_out), NB(dec_jac)};
 }
 #undef NB
@@ -743,6 +745,9 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
   ENSURE(d->row_samp, rowcap, row_samp);
   const int nchunk = std::max(1, std::min(64, 2 * d->num_sms / B));
   ENSURE(d->partials, (size_t)B * 2 * nchunk * QSP_PART_STRIDE, partials);
+  float* reduced = nullptr;                                             // k_reduce_partials: many chunks, few objects
+  const bool pre_reduce = d->pre_reduce >= 0 ? d->pre_reduce != 0 : nchunk >= 8;
+  if (pre_reduce) ENSURE(d->reduced, (size_t)B * 2 * QSP_PART_STRIDE, reduced);
   d_rec = records;
   if (host) ENSURE(d->out_rec, (size_t)B * QSP_RECORD_LEN, d_rec);
   float *dbgH = nullptr, *dbgb = nullptr, *dbgdx = nullptr;
@@ -827,7 +832,12 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
     KL(k_accumulate, dim3(nchunk, B, 2), 256, st, state, d_pts_off, d_rays_off, band_base, M, jp_pts, g_sdf, g_jac,
                                                      row_fac, row_res, p.b2, p.b1, 0, nullptr, partials);
     MARK("k_accumulate");
-    KL(k_solve, B, 256, st, state, d_pts_off, nchunk, partials, p, 0, nullptr, dbgH, dbgb, dbgdx);
+    if (pre_reduce) {
+      KL(k_reduce_partials, dim3((2628 + 255) / 256, 2 * B), 256, st, partials, nchunk, 0, reduced);
+      KL(k_solve, B, 256, st, state, d_pts_off, 1, reduced, p, 0, nullptr, dbgH, dbgb, dbgdx);
+    } else {
+      KL(k_solve, B, 256, st, state, d_pts_off, nchunk, partials, p, 0, nullptr, dbgH, dbgb, dbgdx);
+    }
     MARK("k_solve");
     CK(cudaGetLastError());
     if (d->debug) {  // parity inspection: copy this iteration's normal equations and index lists out
@@ -1116,6 +1126,9 @@ extern "C" int qsp_estimate_pose_batch(qsp_decoder* d, int32_t num_iterations, i
   ENSURE(d->m_active, B, m_active);
   const int nchunk = std::max(1, std::min(64, 2 * d->num_sms / B));
   ENSURE(d->partials, (size_t)B * 2 * nchunk * QSP_PART_STRIDE, partials);
+  float* reduced = nullptr;
+  const bool pre_reduce = d->pre_reduce >= 0 ? d->pre_reduce != 0 : nchunk >= 8;
+  if (pre_reduce) ENSURE(d->reduced, (size_t)B * 2 * QSP_PART_STRIDE, reduced);
   if (host) ENSURE(d->out_rec, (size_t)B * 16, d_out);
   const int tb = 256;
   GnParamsDev p{};
@@ -1129,7 +1142,12 @@ extern "C" int qsp_estimate_pose_batch(qsp_decoder* d, int32_t num_iterations, i
     if ((r = launch_decoder(d, d->precision == QSP_PREC_FP32_CORES ? DEC_FP32 : DEC_SPLIT, true, jp_pts, jp_code, codes_dev, sizeof(ObjState) / 4, M, nullptr, 1, g_sdf, g_jac, st))) return r;
     KL(k_accumulate, dim3(nchunk, B, 1), 256, st, state, d_pts_off, d_pts_off, nullptr, M, jp_pts, g_sdf, g_jac,
                                                      nullptr, nullptr, 0.f, 0.f, 1, row_active, partials);
-    KL(k_solve, B, 256, st, state, d_pts_off, nchunk, partials, p, 1, m_active, nullptr, nullptr, nullptr);
+    if (pre_reduce) {
+      KL(k_reduce_partials, dim3((2628 + 255) / 256, 2 * B), 256, st, partials, nchunk, 1, reduced);
+      KL(k_solve, B, 256, st, state, d_pts_off, 1, reduced, p, 1, m_active, nullptr, nullptr, nullptr);
+    } else {
+      KL(k_solve, B, 256, st, state, d_pts_off, nchunk, partials, p, 1, m_active, nullptr, nullptr, nullptr);
+    }
     if (it == 4) {  // optimizer.py:80-82
       CK(cudaMemsetAsync(m_active, 0, (size_t)B * 4, st));
       KL(k_prune, std::max(1, (M + tb - 1) / tb), tb, st, g_sdf, pt_obj, M, row_active, m_active);
