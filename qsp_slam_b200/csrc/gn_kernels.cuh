@@ -225,18 +225,27 @@ __global__ void k_phase_list(int p, int R, const ObjState* __restrict__ st, cons
   if (lane == 0) ray_nev[r] = start + m;
 }
 
-// exclusive scan of n ints into out[0..n] (out[n] = total); single block, fixed order
+// exclusive scan of n ints into out[0..n] (out[n] = total); single block.  A thread owns SCAN_ITEMS consecutive
+// elements (all its loads in flight together), so 1024 threads cover 8192 elements per pass with one block-wide
+// scan of the thread sums: one pass for a 32-object frame (8192 rays), three barriers per pass.
+#define SCAN_ITEMS 8
 __global__ void k_exclusive_scan(const int* __restrict__ in, int* __restrict__ out, int n,
                                  int* total, int total_add, int* total2) {
   pdl_prologue();
   __shared__ int wsum[32];
   __shared__ int carry_s;
-  int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   if (tid == 0) carry_s = 0;
   __syncthreads();
-  for (int base = 0; base < n; base += blockDim.x) {
-    int i = base + tid;
-    int v = i < n ? in[i] : 0, x = v;
+  for (int base = 0; base < n; base += blockDim.x * SCAN_ITEMS) {
+    const int i0 = base + tid * SCAN_ITEMS;
+    int v[SCAN_ITEMS];
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) v[k] = i0 + k < n ? in[i0 + k] : 0;
+    int mine = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) mine += v[k];
+    int x = mine;
     for (int d = 1; d < 32; d <<= 1) {
       int y = __shfl_up_sync(0xffffffffu, x, d);
       if (lane >= d) x += y;
@@ -252,12 +261,17 @@ __global__ void k_exclusive_scan(const int* __restrict__ in, int* __restrict__ o
       wsum[lane] = t - s;
     }
     __syncthreads();
-    int carry = carry_s;
-    if (i < n) out[i] = carry + wsum[w] + x - v;
+    const int carry = carry_s;
+    int run = carry + wsum[w] + x - mine;               // exclusive prefix of this thread's first element
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) {
+      if (i0 + k < n) out[i0 + k] = run;
+      run += v[k];
+    }
     __syncthreads();
-    if (tid == blockDim.x - 1) carry_s = carry + wsum[w] + x;
-    __syncthreads();
+    if (tid == blockDim.x - 1) carry_s = run;
   }
+  __syncthreads();
   if (tid == 0) {
     out[n] = carry_s;
     if (total) *total = carry_s;
