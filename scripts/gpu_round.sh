@@ -16,8 +16,8 @@ timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --c
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_decoder_ -c 4 -o gpurun_out/decoder_tc -f \
   python scripts/profile_decoder.py $ROWS > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?"
 # the Gauss-Newton kernels (b)-(d) of one warm iteration under ncu --set full (DRAM bytes and throughput per launch)
-timeout 600 ncu --set full --clock-control none -k 'regex:k_(prep|sample|phase_list|candidates|exclusive_scan|surface_xform|refine_scatter|render|row_factors|accumulate|solve)' \
-  --launch-skip 230 -c 26 -o gpurun_out/gn_kernels -f python bench.py --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_gn.log 2>&1; echo "ncu gn rc=$?"
+timeout 600 ncu --set full --clock-control none -k 'regex:k_(prep|sample|phase_list|candidates|exclusive_scan|surface_xform|refine_scatter|render|row_factors|accumulate|reduce_partials|solve)' \
+  --launch-skip 216 -c 20 -o gpurun_out/gn_kernels -f python bench.py --steps 1 --warmup 1 --no-cpu-baseline > gpurun_out/ncu_gn.log 2>&1; echo "ncu gn rc=$?"
 QSP_TIMELINE=1 timeout 200 python scripts/timeline.py 2> gpurun_out/timeline.txt; QSP_TIMELINE=1 timeout 200 python scripts/timeline.py kitti_single 2> gpurun_out/timeline_single.txt
 timeout 600 python scripts/bench_configs.py > gpurun_out/configs.jsonl 2> gpurun_out/configs.err; echo "configs rc=$?"
 ls -la gpurun_out
