@@ -82,3 +82,21 @@ def test_synth_is_deterministic(decoder_state):
     b = synth.make_object(pool, 5, 100, 32, 16)
     assert all(np.array_equal(a[k], b[k]) for k in a)
     assert a["rays"].shape == (48, 3) and np.allclose(a["rays"][:, 2], 1.0) and a["depth"].shape == (32,)
+
+
+def test_pack_accepts_what_pybind11_delivers():
+    """Optimizer._pack (host logic): Fortran-ordered float32 from Eigen, C-ordered float32 / float64 from the Python
+    scripts, empty (0,3) and (0,0) members -> one C-ordered float32 array and int32 offsets."""
+    from qsp_slam_b200.reconstruct.optimizer import Optimizer
+    rng = np.random.default_rng(0)
+    arrs = [np.asfortranarray(rng.standard_normal((5, 3)).astype(np.float32)), np.zeros((0, 3), np.float32),
+            rng.standard_normal((7, 3)), np.zeros((0, 0), np.float32), rng.standard_normal((4, 3)).astype(np.float32)[::2]]
+    cat, off = Optimizer._pack(arrs, 3)
+    ref = np.concatenate([np.ascontiguousarray(a, dtype=np.float32).reshape(-1, 3) for a in arrs])
+    np.testing.assert_array_equal(cat, ref)
+    assert cat.flags.c_contiguous and cat.dtype == np.float32 and off.dtype == np.int32
+    assert off.tolist() == [0, 5, 5, 12, 12, 14]
+    d, o = Optimizer._pack([np.arange(3.0), np.zeros(0), np.arange(2, dtype=np.float32)], 0)
+    assert d.tolist() == [0, 1, 2, 0, 1] and o.tolist() == [0, 3, 3, 5] and d.dtype == np.float32
+    e, o = Optimizer._pack([np.zeros((0, 3), np.float32)], 3)
+    assert e.shape == (0, 3) and o.tolist() == [0, 0]
