@@ -777,7 +777,7 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
   const int cand_blocks = (int)((bandcap + tb - 1) / tb);
   CK(cudaMemsetAsync(counters, 0, (8 + GN_MAXC) * sizeof(int), st));
   int* phase_cnt = counters + 8;
-  const int n_phases = d->phases ? (S + 31) / 32 : 1;
+  const int n_phases = d->phases ? gn_num_phases(S) : 1;
   std::vector<std::pair<const char*, cudaEvent_t>> marks;   // diagnostic timeline of the last iteration
 #define MARK(name)                                                        \
   do {                                                                    \
@@ -801,7 +801,7 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
     // in phases of 32 samples along the ray; a ray stops at its first certainly-opaque sample (k_phase_list)
     if (d->phases) {
       for (int ph = 0; ph < n_phases; ++ph) {
-        KL(k_phase_list, ray_blocks, tb, st, ph, R, state, ray_obj, ray_base, q_sdf, q_code, ray_nev, ph_list, ph_code, phase_cnt);
+        KL(k_phase_list, ray_blocks, tb, st, ph, (int)(ph == n_phases - 1), R, state, ray_obj, ray_base, q_sdf, q_code, ray_nev, ph_list, ph_code, phase_cnt);
         MARK("k_phase_list");
         if ((r = launch_decoder(d, first_mode, false, q_pts, ph_code, codes_dev, code_stride, 0, phase_cnt + ph, 1, q_sdf, nullptr, st, ph_list))) return r;
         MARK("first-pass decoder");

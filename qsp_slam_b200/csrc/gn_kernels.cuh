@@ -192,13 +192,21 @@ __global__ void k_sample(const ObjState* __restrict__ st, const float* __restric
   if (!FILL && lane == 0) ray_cnt[r] = cnt;
 }
 
-// First pass in phases along the ray (front to back).  Phase p decodes in-ball samples [32p, 32p + 32) of every
+// First pass in phases along the ray (front to back).  Phase p decodes in-ball samples [32p, 32p + 32) (the last
+// phase: up to 32 + GN_PHASE_TAIL) of every
 // ray that has not met a certainly-opaque sample (first-pass s <= -lim, hence exact s <= -th and occupancy exactly
 // 1, loss_utils.py:46-47) in an earlier phase: behind such a sample the transmittance cumprod(1 - o) is exactly 0
 // (loss.py:99), so those samples weigh 0 in the rendered depth (:106-114) and have de_do = 0 (:118-125) - their SDF
 // is never needed.  One warp per ray appends its rows to the phase's list (order within the list is irrelevant:
 // the decoder scatters through the list) and records how many of the ray's samples have been decoded.
-__global__ void k_phase_list(int p, int R, const ObjState* __restrict__ st, const int* __restrict__ ray_obj,
+// The last phase also takes a short tail of up to GN_PHASE_TAIL samples (S = 100: phases of 32, 32, 36 instead of a
+// fourth launch pair for 4 samples per ray).
+#define GN_PHASE_TAIL 8
+__host__ __device__ inline int gn_num_phases(int S) {
+  const int full = (S + 31) / 32, rem = S - (full - 1) * 32;
+  return (full > 1 && rem <= GN_PHASE_TAIL) ? full - 1 : full;
+}
+__global__ void k_phase_list(int p, int last, int R, const ObjState* __restrict__ st, const int* __restrict__ ray_obj,
                              const int* __restrict__ ray_base, const float* __restrict__ q_sdf,
                              const int* __restrict__ q_code, int* __restrict__ ray_nev,
                              int* __restrict__ list, int* __restrict__ list_code, int* __restrict__ phase_cnt) {
@@ -214,13 +222,13 @@ __global__ void k_phase_list(int p, int R, const ObjState* __restrict__ st, cons
     const float s = q_sdf[lo + start - 32 + lane];       // the previous phase's 32 samples of this ray
     if (__any_sync(0xffffffffu, s <= -lim) || nev != start) return;
   }
-  const int m = min(32, n - start);
+  const int m = min(last ? 32 + GN_PHASE_TAIL : 32, n - start);
   int base = 0;
   if (lane == 0) base = atomicAdd(phase_cnt + p, m);
   base = __shfl_sync(0xffffffffu, base, 0);
-  if (lane < m) {
-    list[base + lane] = lo + start + lane;
-    list_code[base + lane] = q_code[lo + start + lane];
+  for (int k = lane; k < m; k += 32) {
+    list[base + k] = lo + start + k;
+    list_code[base + k] = q_code[lo + start + k];
   }
   if (lane == 0) ray_nev[r] = start + m;
 }
