@@ -1,8 +1,10 @@
-"""TEST INFRASTRUCTURE ONLY - imports the UNMODIFIED reference hot path from /root/reference.
+"""TEST INFRASTRUCTURE ONLY - imports the UNMODIFIED reference hot path.
 
-This works only in the build container (``/root/reference`` does not exist on the GPU box), and
-is used for exactly two things: validating the restatement in ``oracle/gn_oracle.py`` and
-generating the golden vectors under ``tests/golden/`` (see ``oracle/make_golden.py``).
+In the build container the modules come from ``/root/reference`` (source); on the GPU box, where that
+directory does not exist, from ``oracle/_ref`` - the same files byte-compiled by ``oracle/build_ref.py``
+(sourceless ``.pyc`` modules, git-ignored, shipped with the snapshot).  Used for: validating the restatement in
+``oracle/gn_oracle.py``, generating the golden vectors under ``tests/golden/`` (``oracle/make_golden.py``), the
+reference arm of ``bench.py`` and the GPU parity tests that compare against the reference itself.
 Nothing in the product package imports this file.
 
 Harness steps:
@@ -20,10 +22,20 @@ import types
 import warnings
 
 REFERENCE_ROOT = "/root/reference"
+COMPILED_ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
+
+
+def reference_root():
+    """Directory to import the reference from: its sources if present, else the byte-compiled copy."""
+    if os.path.isfile(os.path.join(REFERENCE_ROOT, "reconstruct", "optimizer.py")):
+        return REFERENCE_ROOT
+    if os.path.isfile(os.path.join(COMPILED_ROOT, "reconstruct", "optimizer.pyc")):
+        return COMPILED_ROOT
+    return None
 
 
 def available() -> bool:
-    return os.path.isfile(os.path.join(REFERENCE_ROOT, "reconstruct", "optimizer.py"))
+    return reference_root() is not None
 
 
 class _AttrDict(dict):
@@ -63,8 +75,9 @@ def load():
     global _loaded
     if _loaded is not None:
         return _loaded
-    if not available():
-        raise RuntimeError("/root/reference is not present on this machine")
+    root = reference_root()
+    if root is None:
+        raise RuntimeError("neither /root/reference nor oracle/_ref (python -m oracle.build_ref) is present")
     import torch
 
     addict = types.ModuleType("addict")
@@ -82,7 +95,7 @@ def load():
     torch.cuda.synchronize = lambda *a, **k: None
     torch.cuda.empty_cache = lambda *a, **k: None
 
-    for p in (REFERENCE_ROOT, os.path.join(REFERENCE_ROOT, "reconstruct")):
+    for p in (root, os.path.join(root, "reconstruct")):
         if p not in sys.path:
             sys.path.insert(0, p)
     warnings.filterwarnings("ignore")
@@ -93,7 +106,7 @@ def load():
     import deep_sdf.deep_sdf_decoder as r_dec
 
     ns = types.SimpleNamespace(optimizer=r_opt, loss=r_loss, loss_utils=r_lu, utils=r_utils,
-                               decoder=r_dec, torch=torch)
+                               decoder=r_dec, torch=torch, root=root)
     _loaded = ns
     return ns
 

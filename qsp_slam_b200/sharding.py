@@ -38,6 +38,76 @@ def balanced_order(costs: Sequence[float], world_size: int) -> List[List[int]]:
     return [sorted(r) for r in ranks]
 
 
+def balanced_equal_counts(costs: Sequence[float], world_size: int) -> List[List[int]]:
+    """Like ``balanced_order`` but every rank gets the same NUMBER of objects (sizes differ by at most one): objects
+    sorted by cost are dealt out in a snake (0..R-1, R-1..0, ...), which keeps the per-rank cost sums within one
+    object's cost of each other.  Used for weak scaling, where the count per GPU is fixed."""
+    order = sorted(range(len(costs)), key=lambda i: (-costs[i], i))
+    ranks: List[List[int]] = [[] for _ in range(world_size)]
+    for k, i in enumerate(order):
+        lap, pos = divmod(k, world_size)
+        ranks[pos if lap % 2 == 0 else world_size - 1 - pos].append(i)
+    return [sorted(r) for r in ranks]
+
+
+def inball_cost(detection: dict, num_depth_samples: int) -> float:
+    """Host-side proxy of an object's work: the number of depth samples of its rays that fall inside the unit ball at
+    the INITIAL pose (what the first decoder pass of the first iteration evaluates, loss.py:60-70), computed
+    analytically per ray (segment of the ray inside the ball / sample spacing).  Cheap (numpy, O(rays))."""
+    T = np.asarray(detection["t_cam_obj"], np.float64).reshape(4, 4)
+    rays = np.asarray(detection["rays"], np.float64).reshape(-1, 3)
+    if rays.shape[0] == 0:
+        return 0.0
+    T_oc = np.linalg.inv(T)
+    R, t = T_oc[:3, :3], T_oc[:3, 3]
+    scale = np.cbrt(np.linalg.det(T[:3, :3]))
+    d_min, d_max = T[2, 3] - scale, T[2, 3] + scale
+    u = rays @ R.T                                    # x_o(d) = d * u + t
+    a = (u * u).sum(1)
+    b = 2.0 * (u @ t)
+    c = float(t @ t) - 1.0
+    disc = b * b - 4.0 * a * c
+    ok = disc > 0
+    sq = np.sqrt(np.where(ok, disc, 0.0))
+    lo = np.maximum((-b - sq) / (2 * a), d_min)
+    hi = np.minimum((-b + sq) / (2 * a), d_max)
+    seg = np.where(ok, np.maximum(hi - lo, 0.0), 0.0)
+    return float(seg.sum() / max(d_max - d_min, 1e-12) * (num_depth_samples - 1))
+
+
+class RecordGatherer:
+    """All-gather of per-rank record blocks with PREALLOCATED buffers (no per-step zeros / empty / cat): ``counts[r]``
+    records of 82 floats from rank r, padded to the maximum.  ``gather(local)`` enqueues one
+    ``all_gather_into_tensor`` on the current stream and returns the (world * max, 82) buffer; ``ordered()`` gives the
+    rows in rank order without the padding (a copy only when the counts are ragged)."""
+
+    def __init__(self, counts: Sequence[int], device, group=None):
+        import torch
+        import torch.distributed as dist
+        self.counts = list(counts)
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.mx = max(self.counts) if self.counts else 0
+        self.pad = torch.zeros((self.mx, RECORD_LEN), dtype=torch.float32, device=device)
+        self.out = torch.empty((self.world * self.mx, RECORD_LEN), dtype=torch.float32, device=device)
+        self.ragged = any(c != self.mx for c in self.counts)
+
+    def gather(self, local_records):
+        import torch.distributed as dist
+        src = local_records
+        if local_records.shape[0] != self.mx:
+            self.pad[: local_records.shape[0]].copy_(local_records)
+            src = self.pad
+        dist.all_gather_into_tensor(self.out, src, group=self.group)
+        return self.out
+
+    def ordered(self):
+        import torch
+        if not self.ragged:
+            return self.out
+        return torch.cat([self.out[r * self.mx: r * self.mx + self.counts[r]] for r in range(self.world)], 0)
+
+
 def gather_records(local_records, counts: Sequence[int], group=None):
     """All-gather per-rank record blocks (n_r, 82) into (sum n_r, 82) in rank order.  ``local_records``
     is a torch tensor on the rank's device (CUDA for NCCL, CPU for gloo).  Ragged counts are handled
