@@ -88,6 +88,10 @@ int qsp_set_first_pass_margin(qsp_decoder* dec, float margin0, float margin_per_
  * allocated at exactly the size the call asked for, between two 256-byte canary bands.  This call synchronises the
  * device and returns how many buffers had a band overwritten (names in qsp_last_error()), 0 if none, -1 if the
  * handle holds no guarded buffer.                                                                              */
+/* Threading: every entry point that takes a handle holds the handle's mutex for the duration of the call (the
+ * workspace is shared), so calls on ONE handle are serialised - as the reference's were by the GIL
+ * (include/System.h:61-75) - and asynchronous calls on one handle must use one stream.  Use one handle per
+ * concurrent stream / thread for parallelism.                                                                   */
 int qsp_check_guards(qsp_decoder* dec);
 /* Positive control for the above: writes one byte just past the first guarded buffer of the handle. */
 int qsp_guard_selftest(qsp_decoder* dec);
@@ -115,6 +119,15 @@ int qsp_reconstruct_batch(qsp_decoder* dec, const qsp_gn_params* prm, int32_t B,
                           const float* rays, const int32_t* rays_off,
                           const float* depth, const int32_t* depth_off,
                           float* records, uint32_t flags, void* stream);
+
+/* Diagnostics of the last qsp_reconstruct_batch call on this handle (no reference counterpart; the reference has no
+ * capacity limits and evaluates every sample in fp32).  The boundary never raises for a numeric or capacity problem
+ * (an exception would terminate the SLAM process): objects whose candidate rows did not fit the row
+ * buffers come back with is_good = 0 and `overflow` != 0 here; `max_first_pass_error` is the largest
+ * |fp16 first pass - fp32-equivalent| SDF seen on a re-evaluated sample and `n_margin_excursions` counts the samples
+ * where it exceeded 3/4 of the object's margin - any > 0 says the margin is too tight for this decoder's weights
+ * (qsp_set_first_pass_margin).  Synchronises the device unless the call was a host-pointer call.                  */
+int qsp_get_call_stats(qsp_decoder* dec, int32_t* overflow, float* max_first_pass_error, int32_t* n_margin_excursions);
 
 /* --- pose-only GN: replaces Optimizer.estimate_pose_cam_obj (optimizer.py:47-93), batched ----- */
 /* t_co_se3 (B,16) SE(3), scale (B), codes (B,64); out (B,16) SE(3) object->camera.             */

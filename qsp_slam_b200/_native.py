@@ -2,6 +2,7 @@
 or no B200 is present, calls raise."""
 from __future__ import annotations
 
+import contextlib
 import ctypes as C
 import os
 
@@ -23,7 +24,7 @@ JAC_STRIDE = 68
 RECORD_LEN = 82
 
 EXPORTS = ["qsp_decoder_create", "qsp_decoder_destroy", "qsp_decode_sdf", "qsp_decode_sdf_jacobian",
-           "qsp_reconstruct_batch", "qsp_estimate_pose_batch", "qsp_set_precision", "qsp_set_first_pass_margin", "qsp_check_guards", "qsp_guard_selftest", "qsp_set_debug", "qsp_get_iteration",
+           "qsp_reconstruct_batch", "qsp_get_call_stats", "qsp_estimate_pose_batch", "qsp_set_precision", "qsp_set_first_pass_margin", "qsp_check_guards", "qsp_guard_selftest", "qsp_set_debug", "qsp_get_iteration",
            "qsp_get_band_indices", "qsp_get_loss_rows", "qsp_rotation_prior", "qsp_exp_map", "qsp_robust_res", "qsp_sdf_to_occupancy", "qsp_point_pose_jacobian", "qsp_mesh_extract", "qsp_set_voxel_grid", "qsp_extract_mesh", "qsp_mesh_sizes", "qsp_mesh_copy", "qsp_mesh_free", "qsp_last_error", "qsp_launch_count", "qsp_kernel_ms", "qsp_version"]
 
 _f32p = C.POINTER(C.c_float)
@@ -49,14 +50,31 @@ class NativeError(RuntimeError):
 _lib = None
 
 
+@contextlib.contextmanager
+def use_library(path: str):
+    """Tests only: bind the package to another build of the library (``libqsp_recon_exp.so``, which also carries the
+    superseded decoder kernels) for the duration of the block.  Handles created inside must be closed inside."""
+    global _lib
+    old = _lib
+    _lib = _load(path)
+    try:
+        yield _lib
+    finally:
+        _lib = old
+
+
 def lib():
     global _lib
-    if _lib is not None:
-        return _lib
-    if not os.path.isfile(LIB_PATH):
-        raise NativeError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+    if _lib is None:
+        _lib = _load(LIB_PATH)
+    return _lib
+
+
+def _load(path: str):
+    if not os.path.isfile(path):
+        raise NativeError(f"{path} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
                           "(there is no CPU fallback)")
-    L = C.CDLL(LIB_PATH)
+    L = C.CDLL(path)
     vp = C.c_void_p
     L.qsp_decoder_create.argtypes = [C.POINTER(DecoderWeights), C.c_int, C.POINTER(vp)]
     L.qsp_decoder_destroy.argtypes = [vp]
@@ -66,6 +84,7 @@ def lib():
     L.qsp_reconstruct_batch.argtypes = [vp, C.POINTER(GnParams), C.c_int32, vp, vp, vp, _i32p, vp, _i32p,
                                         vp, _i32p, vp, C.c_uint32, vp]
     L.qsp_estimate_pose_batch.argtypes = [vp, C.c_int32, C.c_int32, vp, vp, vp, vp, _i32p, vp, C.c_uint32, vp]
+    L.qsp_get_call_stats.argtypes = [vp, _i32p, _f32p, _i32p]
     L.qsp_set_debug.argtypes = [vp, C.c_int32]
     L.qsp_set_precision.argtypes = [vp, C.c_int32]
     L.qsp_set_first_pass_margin.argtypes = [vp, C.c_float, C.c_float]
@@ -90,7 +109,6 @@ def lib():
     L.qsp_launch_count.restype = C.c_int64
     L.qsp_kernel_ms.argtypes = [vp, _f32p]
     L.qsp_version.restype = C.c_char_p
-    _lib = L
     return L
 
 

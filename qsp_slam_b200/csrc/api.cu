@@ -2,7 +2,9 @@
 // per-iteration launch sequence.  Host code only orchestrates; all arithmetic is in the kernels.
 #include <cuda_fp16.h>
 #include <atomic>
+#include <climits>
 #include <cmath>
+#include <mutex>
 #include <cstdio>
 #include <cstring>
 #include <cstdlib>
@@ -13,7 +15,13 @@
 #include "../../include/qsp_recon.h"
 #include "decoder_ffma.cuh"
 #include "decoder_tc.cuh"
+// Superseded decoder kernels (measured negative results): the transposed three-product kernel
+// k_decoder_t3, the four-product TC_SPLIT mode of k_decoder_tc and the single-CTA variants.  Built only with
+// -DQSP_EXPERIMENTAL (libqsp_recon_exp.so, used by the A/B tests); the product library carries
+// k_decoder_tc<TC_FAST> (CTA pairs), k_decoder_p3 and k_decoder_ffma only.
+#ifdef QSP_EXPERIMENTAL
 #include "decoder_t3.cuh"
+#endif
 #include "decoder_p3.cuh"
 #include "gn_kernels.cuh"
 #include "mesh_kernels.cuh"
@@ -76,6 +84,7 @@ struct IterDebug {
 };
 
 struct qsp_decoder {
+  std::mutex mu;                       // one call at a time per handle: the workspace below is shared by all entry points
   int device = 0;
   int num_sms = 148;
   DecoderDev dw{};
@@ -90,7 +99,7 @@ struct qsp_decoder {
   Buf grid_pts, grid_sdf, grid_need, grid_list, grid_cnt, grid_code;   // qsp_extract_mesh
   int grid_D = 0;
   Buf jp_pts, jp_code, g_sdf, g_jac, row_fac, row_res, row_ray, row_samp, row_active, m_active;
-  Buf partials, reduced, dbgH, dbgb, dbgdx;
+  Buf partials, reduced, dbgH, dbgb, dbgdx, blk_tot, blk_base;
   Buf dec_pts, dec_codes, dec_out, dec_jac;
   bool debug = false;
   std::vector<IterDebug> dbg;
@@ -107,7 +116,18 @@ struct qsp_decoder {
   bool phases = true;                              // first pass front to back in phases of 32 samples per ray
   int pre_reduce = -1;                             // QSP_REDUCE=0/1: k_reduce_partials before k_solve (default: when >= 8 chunks)
   bool timeline = false;                           // QSP_TIMELINE=1: CUDA-event time of every launch group of one GN iteration
+  bool fused = true;                               // QSP_FUSED=0: the unfused small-kernel sequence (A/B, bit-identical results)
+  bool concurrent = true;                          // QSP_CONCURRENT=0: never split the surface rows onto the side stream
+  long band_cap = 0;                               // QSP_BAND_CAP=n (debug): candidate row capacity, to exercise the overflow path
+  cudaStream_t side = nullptr;                     // surface-row decoder launch of small batches, concurrent with the first pass
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  // diagnostics of the last qsp_reconstruct_batch call: candidate overflow flag, max |first pass - exact| (float
+  // bits), candidates whose first-pass error exceeded 3/4 of the margin; valid once the call has been synchronised
+  int last_stats[3] = {0, 0, 0};
+  const int* stats_dev = nullptr;
+  bool stats_fresh = false;
 };
+#define LOCK(d) std::lock_guard<std::mutex> lock_((d)->mu)
 
 template <typename T>
 static int ensure(Buf& b, size_t n, T** out) {
@@ -219,6 +239,7 @@ static int build_tc_images(qsp_decoder* d, const std::vector<std::vector<float>>
         }
       }
   }
+#ifdef QSP_EXPERIMENTAL
   // k_decoder_t3 stream: 128-row A-operand images in the order (step, half, k-block, M-tile, hi then lo)
   std::vector<__half> t3;
   for (int s = 0; s < 16; ++s) {
@@ -240,11 +261,15 @@ static int build_tc_images(qsp_decoder* d, const std::vector<std::vector<float>>
             }
         }
   }
-  void *pf = nullptr, *ps = nullptr, *pt = nullptr;
-  CK(cudaMalloc(&pt, t3.size() * 2));
-  d->weight_allocs.push_back(pt);
-  CK(cudaMemcpy(pt, t3.data(), t3.size() * 2, cudaMemcpyHostToDevice));
-  d->tc.img_t3 = reinterpret_cast<const uint8_t*>(pt);
+  {
+    void* pt = nullptr;
+    CK(cudaMalloc(&pt, t3.size() * 2));
+    d->weight_allocs.push_back(pt);
+    CK(cudaMemcpy(pt, t3.data(), t3.size() * 2, cudaMemcpyHostToDevice));
+    d->tc.img_t3 = reinterpret_cast<const uint8_t*>(pt);
+  }
+#endif
+  void *pf = nullptr, *ps = nullptr;
   CK(cudaMalloc(&pf, fast.size() * 2));
   d->weight_allocs.push_back(pf);
   CK(cudaMalloc(&ps, split.size() * 2));
@@ -266,8 +291,8 @@ extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_
   CK(cudaSetDevice(device));
   cudaDeviceProp prop;
   CK(cudaGetDeviceProperties(&prop, device));
-  if (prop.major < 10) {
-    g_err = "device is not sm_100: this library is built for B200 only";
+  if (prop.major != 10 || prop.minor != 0) {                // the cubin is sm_100a only: no PTX, no other architecture
+    g_err = "device is not sm_100 (B200): this library is built for sm_100a only";
     return QSP_ERR_NO_DEVICE;
   }
   qsp_decoder* d = new qsp_decoder();
@@ -309,17 +334,9 @@ extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_
   if ((r = build_tc_images(d, Wall)) || (r = upload(d, bias_all, &d->tc.bias))) { qsp_decoder_destroy(d); return r; }
   d->tc.w8 = d->dw.w8;
   d->tc.b8 = d->dw.b8;
-  CK(cudaFuncSetAttribute(k_decoder_tc<TC_FAST, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-  CK(cudaFuncSetAttribute(k_decoder_tc<TC_SPLIT, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-  CK(cudaFuncSetAttribute(k_decoder_tc<TC_SPLIT, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
   CK(cudaFuncSetAttribute(k_decoder_tc<TC_FAST, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-  CK(cudaFuncSetAttribute(k_decoder_tc<TC_SPLIT, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-  CK(cudaFuncSetAttribute(k_decoder_tc<TC_SPLIT, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
   CK(cudaFuncSetAttribute(k_decoder_p3<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
   CK(cudaFuncSetAttribute(k_decoder_p3<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-  if (const char* e2 = getenv("QSP_TC_PAIR")) d->pair = atoi(e2) != 0;
-  if (const char* e3 = getenv("QSP_TC_P3")) d->p3 = atoi(e3) != 0;       // three-product CTA-pair kernel k_decoder_p3
-  d->t3 = getenv("QSP_TC_T3") != nullptr;             // A/B switch: the transposed three-product kernel k_decoder_t3
   {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(d->num_sms / 2 * 2));
@@ -330,9 +347,18 @@ extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_
     at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
     cfg.attrs = at; cfg.numAttrs = 1;
     int ncl = 0;
-    cudaError_t e = cudaOccupancyMaxActiveClusters(&ncl, k_decoder_tc<TC_SPLIT, true, 2>, &cfg);
+    cudaError_t e = cudaOccupancyMaxActiveClusters(&ncl, k_decoder_p3<true>, &cfg);
     d->pair_grid = (e == cudaSuccess && ncl > 0) ? ncl * 2 : d->num_sms / 2 * 2;
   }
+#ifdef QSP_EXPERIMENTAL
+  CK(cudaFuncSetAttribute(k_decoder_tc<TC_FAST, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+  CK(cudaFuncSetAttribute(k_decoder_tc<TC_SPLIT, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+  CK(cudaFuncSetAttribute(k_decoder_tc<TC_SPLIT, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+  CK(cudaFuncSetAttribute(k_decoder_tc<TC_SPLIT, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+  CK(cudaFuncSetAttribute(k_decoder_tc<TC_SPLIT, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+  if (const char* e2 = getenv("QSP_TC_PAIR")) d->pair = atoi(e2) != 0;
+  if (const char* e3 = getenv("QSP_TC_P3")) d->p3 = atoi(e3) != 0;       // three-product CTA-pair kernel k_decoder_p3
+  d->t3 = getenv("QSP_TC_T3") != nullptr;             // A/B switch: the transposed three-product kernel k_decoder_t3
   CK(cudaFuncSetAttribute(k_decoder_t3<false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, T3_SMEM_BYTES));
   CK(cudaFuncSetAttribute(k_decoder_t3<true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, T3_SMEM_BYTES));
   CK(cudaFuncSetAttribute(k_decoder_t3<false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, T3_SMEM_BYTES));
@@ -358,17 +384,24 @@ extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_
     d->t3_grid = (e == cudaSuccess && ncl > 0) ? ncl * d->cluster : d->num_sms / d->cluster * d->cluster;
     if (getenv("QSP_TC_VERBOSE")) fprintf(stderr, "qsp: t3 cluster %d, %d co-resident clusters, grid %d\n", d->cluster, ncl, d->t3_grid);
   }
+#endif
   CK(cudaFuncSetAttribute(k_decoder_ffma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FF_SMEM_BYTES));
   CK(cudaFuncSetAttribute(k_decoder_ffma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FF_SMEM_BYTES));
   if (const char* e = getenv("QSP_PHASES")) d->phases = atoi(e) != 0;
   if (const char* e = getenv("QSP_TIMELINE")) d->timeline = atoi(e) != 0;
   if (const char* e = getenv("QSP_REDUCE")) d->pre_reduce = atoi(e) != 0;
+  if (const char* e = getenv("QSP_FUSED")) d->fused = atoi(e) != 0;
+  if (const char* e = getenv("QSP_CONCURRENT")) d->concurrent = atoi(e) != 0;
+  if (const char* e = getenv("QSP_BAND_CAP")) d->band_cap = atol(e);
   if (const char* dbg_env = getenv("QSP_TC_DEBUG")) {
     int v = atoi(dbg_env);
     CK(cudaMemcpyToSymbol(g_tc_dbg, &v, sizeof(int)));
   }
   CK(cudaEventCreate(&d->ev0));
   CK(cudaEventCreate(&d->ev1));
+  CK(cudaStreamCreateWithFlags(&d->side, cudaStreamNonBlocking));
+  CK(cudaEventCreateWithFlags(&d->ev_fork, cudaEventDisableTiming));
+  CK(cudaEventCreateWithFlags(&d->ev_join, cudaEventDisableTiming));
   *out = d;
   return QSP_OK;
 }
@@ -381,7 +414,7 @@ static std::vector<std::pair<const char*, Buf*>> all_bufs(qsp_decoder* d) {
           NB(band_cnt), NB(band_base), NB(q_pts), NB(q_code), NB(q_samp), NB(cand_q), NB(q_sdf), NB(slot), NB(ray_res),
           NB(ray_nev), NB(ph_list), NB(ph_code), NB(grid_pts), NB(grid_sdf), NB(grid_need), NB(grid_list), NB(grid_cnt),
           NB(grid_code), NB(jp_pts), NB(jp_code), NB(g_sdf), NB(g_jac), NB(row_fac), NB(row_res), NB(row_ray),
-          NB(row_samp), NB(row_active), NB(m_active), NB(partials), NB(reduced), NB(dbgH), NB(dbgb), NB(dbgdx), NB(dec_pts),
+          NB(row_samp), NB(row_active), NB(m_active), NB(partials), NB(reduced), NB(dbgH), NB(dbgb), NB(dbgdx), NB(blk_tot), NB(blk_base), NB(dec_pts),
           NB(dec_codes), NB(dec_out), NB(dec_jac)};
 }
 #undef NB
@@ -390,6 +423,7 @@ static std::vector<std::pair<const char*, Buf*>> all_bufs(qsp_decoder* d) {
 // overwritten (their names in qsp_last_error()), 0 if all are intact, -1 if no buffer is guarded.
 extern "C" int qsp_check_guards(qsp_decoder* d) {
   if (!d) { g_err = "null handle"; return QSP_ERR_INVALID; }
+  LOCK(d);
   cudaSetDevice(d->device);
   if (cudaDeviceSynchronize() != cudaSuccess) { g_err = "cudaDeviceSynchronize failed"; return QSP_ERR_CUDA; }
   int bad = 0, seen = 0;
@@ -418,6 +452,7 @@ extern "C" int qsp_check_guards(qsp_decoder* d) {
 // Debug: positive control for qsp_check_guards - writes one byte just past the first guarded buffer.
 extern "C" int qsp_guard_selftest(qsp_decoder* d) {
   if (!d) { g_err = "null handle"; return QSP_ERR_INVALID; }
+  LOCK(d);
   cudaSetDevice(d->device);
   for (auto& nb : all_bufs(d)) {
     Buf* b = nb.second;
@@ -437,17 +472,22 @@ extern "C" void qsp_decoder_destroy(qsp_decoder* d) {
     if (nb.second->raw) cudaFree(nb.second->raw);
   if (d->ev0) cudaEventDestroy(d->ev0);
   if (d->ev1) cudaEventDestroy(d->ev1);
+  if (d->ev_fork) cudaEventDestroy(d->ev_fork);
+  if (d->ev_join) cudaEventDestroy(d->ev_join);
+  if (d->side) cudaStreamDestroy(d->side);
   delete d;
 }
 
 extern "C" int qsp_set_precision(qsp_decoder* d, int32_t precision) {
   if (!d || (precision != QSP_PREC_TENSOR && precision != QSP_PREC_FP32_CORES)) { g_err = "bad precision"; return QSP_ERR_INVALID; }
+  LOCK(d);
   d->precision = precision;
   return QSP_OK;
 }
 
 extern "C" int qsp_set_first_pass_margin(qsp_decoder* d, float margin0, float margin_per_norm) {
   if (!d || !(margin0 >= 0.f) || !(margin_per_norm >= 0.f)) { g_err = "bad argument"; return QSP_ERR_INVALID; }
+  LOCK(d);
   d->margin0 = margin0;
   d->margin1 = margin_per_norm;
   return QSP_OK;
@@ -484,6 +524,7 @@ static int launch_clustered(K kernel, int grid, int cl, size_t smem, cudaStream_
   return QSP_OK;
 }
 
+#ifdef QSP_EXPERIMENTAL
 // k_decoder_t3 as thread-block clusters of d->cluster CTAs that share one multicast weight stream
 template <bool JAC, int CL>
 static int launch_t3_cl(int grid, const TcDecoderDev& tc, const float* pts, const int* code_idx, const float* codes,
@@ -510,42 +551,55 @@ static int launch_t3(qsp_decoder* d, bool jac, int grid, const float* pts, const
 #undef T3_CASE
 }
 
+#endif
+
+// grid_cap > 0 limits the persistent grid (small batches: the surface rows run on the side stream next to the
+// first pass, each on its own share of the SMs)
 static int launch_decoder(qsp_decoder* d, int mode, bool jac, const float* pts, const int* code_idx, const float* codes,
                           int code_stride, long n, const int* n_dev, int n_codes_y, float* sdf, float* jacp,
-                          cudaStream_t st, const int* row_map = nullptr) {
-  if (row_map && (jac || d->t3 || n_codes_y != 1)) { g_err = "row_map: single-code forward passes only"; return QSP_ERR_INVALID; }
+                          cudaStream_t st, const int* row_map = nullptr, int grid_cap = 0) {
+  bool t3 = false;
+#ifdef QSP_EXPERIMENTAL
+  t3 = d->t3;
+#endif
+  if (row_map && (jac || t3 || n_codes_y != 1)) { g_err = "row_map: single-code forward passes only"; return QSP_ERR_INVALID; }
   TcDecoderDev tc = d->tc;
   tc.row_map = row_map;
   const int rows_per_tile = mode == DEC_FAST ? 128 : 64;
   long tiles = n_dev ? (long)d->num_sms : ((n + rows_per_tile - 1) / rows_per_tile) * n_codes_y;
   if (tiles <= 0) return QSP_OK;
   dim3 grid((unsigned)std::min<long>(tiles, d->num_sms));   // persistent: one CTA per SM
+  if (grid_cap > 0) grid.x = std::min<unsigned>(grid.x, (unsigned)grid_cap);
   if (mode != DEC_FP32) {
+    const int pgrid = std::min<int>(grid.x, d->pair_grid);
+    int r_ = QSP_OK;
+#ifdef QSP_EXPERIMENTAL
 #define TC_LAUNCH(M, J)                                                                                              \
-  do {                                                                                                               \
-    int r_ = d->pair ? launch_clustered(k_decoder_tc<M, J, 2>, std::min<int>(grid.x, d->pair_grid), 2, TC_SMEM_BYTES, st, tc, pts, \
-                                        code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp)               \
-                     : launch_clustered(k_decoder_tc<M, J, 1>, grid.x, 1, TC_SMEM_BYTES, st, tc, pts, code_idx, codes, \
-                                        code_stride, n_codes_y, n, n_dev, sdf, jacp);                               \
-    if (r_) return r_;                                                                                               \
-  } while (0)
+    r_ = d->pair ? launch_clustered(k_decoder_tc<M, J, 2>, pgrid, 2, TC_SMEM_BYTES, st, tc, pts,                    \
+                                    code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp)                    \
+                 : launch_clustered(k_decoder_tc<M, J, 1>, grid.x, 1, TC_SMEM_BYTES, st, tc, pts, code_idx, codes,   \
+                                    code_stride, n_codes_y, n, n_dev, sdf, jacp)
     if (mode == DEC_FAST && !jac)
       TC_LAUNCH(TC_FAST, false);
-    else if (d->p3 && d->pair) {
-      int r_ = jac ? launch_clustered(k_decoder_p3<true>, std::min<int>(grid.x, d->pair_grid), 2, TC_SMEM_BYTES, st, tc, pts, code_idx,
-                                      codes, code_stride, n_codes_y, n, n_dev, sdf, jacp)
-                   : launch_clustered(k_decoder_p3<false>, std::min<int>(grid.x, d->pair_grid), 2, TC_SMEM_BYTES, st, tc, pts, code_idx,
-                                      codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
-      if (r_) return r_;
-    } else if (d->t3) {
-      int r = launch_t3(d, jac, grid.x, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp, st);
-      if (r) return r;
-    }
+    else if (d->p3 && d->pair)
+      r_ = jac ? launch_clustered(k_decoder_p3<true>, pgrid, 2, TC_SMEM_BYTES, st, tc, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp)
+               : launch_clustered(k_decoder_p3<false>, pgrid, 2, TC_SMEM_BYTES, st, tc, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
+    else if (d->t3)
+      r_ = launch_t3(d, jac, grid.x, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp, st);
     else if (!jac)
       TC_LAUNCH(TC_SPLIT, false);
     else
       TC_LAUNCH(TC_SPLIT, true);
 #undef TC_LAUNCH
+#else
+    if (mode == DEC_FAST && !jac)
+      r_ = launch_clustered(k_decoder_tc<TC_FAST, false, 2>, pgrid, 2, TC_SMEM_BYTES, st, tc, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
+    else if (jac)
+      r_ = launch_clustered(k_decoder_p3<true>, pgrid, 2, TC_SMEM_BYTES, st, tc, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
+    else
+      r_ = launch_clustered(k_decoder_p3<false>, pgrid, 2, TC_SMEM_BYTES, st, tc, pts, code_idx, codes, code_stride, n_codes_y, n, n_dev, sdf, jacp);
+#endif
+    if (r_) return r_;
     LAUNCHED();
     CK(cudaGetLastError());
     return QSP_OK;
@@ -564,6 +618,7 @@ static int launch_decoder(qsp_decoder* d, int mode, bool jac, const float* pts, 
 extern "C" int qsp_decode_sdf(qsp_decoder* d, const float* codes, int32_t n_codes, const float* pts,
                               int64_t n, float* out, uint32_t flags, void* stream) {
   if (!d || !codes || !pts || !out || n_codes <= 0 || n < 0) { g_err = "bad argument"; return QSP_ERR_INVALID; }
+  LOCK(d);
   CK(cudaSetDevice(d->device));
   cudaStream_t st = (cudaStream_t)stream;
   const float *dc = codes, *dp = pts;
@@ -596,6 +651,7 @@ extern "C" int qsp_decode_sdf(qsp_decoder* d, const float* codes, int32_t n_code
 extern "C" int qsp_decode_sdf_jacobian(qsp_decoder* d, const float* code, const float* pts, int64_t n,
                                        float* sdf, float* jac, uint32_t flags, void* stream) {
   if (!d || !code || !pts || !sdf || !jac || n < 0) { g_err = "bad argument"; return QSP_ERR_INVALID; }
+  LOCK(d);
   CK(cudaSetDevice(d->device));
   cudaStream_t st = (cudaStream_t)stream;
   const float *dc = code, *dp = pts;
@@ -671,6 +727,7 @@ static int check_offsets(const int32_t* off, int B, const char* name) {
 
 extern "C" int qsp_set_debug(qsp_decoder* d, int32_t on) {
   if (!d) return QSP_ERR_INVALID;
+  LOCK(d);
   d->debug = on != 0;
   d->dbg.clear();
   return QSP_OK;
@@ -696,12 +753,18 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
       g_err = "more depth values than rays";
       return QSP_ERR_INVALID;
     }
+  LOCK(d);
   CK(cudaSetDevice(d->device));
   cudaStream_t st = (cudaStream_t)stream;
   const bool host = flags & QSP_FLAG_HOST_PTRS;
   const int M = pts_off[B], R = rays_off[B], K = depth_off[B];
   const size_t qcap = (size_t)R * S;
-  const size_t bandcap = qcap / 4 + 4096;
+  // Candidate rows: any in-ball sample can become one (a wide cut_off band), so the row buffers take them all while
+  // that stays below ~6 GB (a 1000-object call); beyond, a quarter - and should a call ever need more, the objects
+  // that do not fit fail (is_good = 0, overflow flag in qsp_get_call_stats), nothing is truncated silently.
+  const size_t row_bytes = (size_t)(QSP_JSTRIDE + 9) * 4;
+  size_t bandcap = ((size_t)M + qcap) * row_bytes <= ((size_t)6 << 30) ? qcap : qcap / 4 + 4096;
+  if (d->band_cap > 0) bandcap = (size_t)d->band_cap;
   const size_t rowcap = (size_t)M + bandcap;
 
   Inputs in{};
@@ -714,9 +777,10 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
   if ((r = stage_off(d->pts_off, pts_off, B, st, &d_pts_off)) || (r = stage_off(d->rays_off, rays_off, B, st, &d_rays_off)) ||
       (r = stage_off(d->depth_off, depth_off, B, st, &d_depth_off))) return r;
 
-  ObjState* state; int *counters, *ray_obj, *pt_obj, *ray_cnt, *ray_base, *band_cnt, *band_base;
+  ObjState* state; int *counters, *ray_obj, *pt_obj, *ray_cnt, *ray_base, *band_cnt, *band_base, *blk_tot, *blk_base;
   float *q_pts, *q_sdf, *slot, *ray_res, *jp_pts, *g_sdf, *g_jac, *row_fac, *row_res, *partials, *d_rec;
   int *q_code, *q_samp, *cand_q, *jp_code, *row_ray, *row_samp, *ray_nev, *ph_list, *ph_code;
+  const int nblk = std::max(1, (R + GN_RAYS_PER_BLOCK - 1) / GN_RAYS_PER_BLOCK);
   ENSURE(d->state, B, state);
   ENSURE(d->counters, 8 + GN_MAXC, counters);
   ENSURE(d->ray_nev, R, ray_nev);
@@ -728,6 +792,8 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
   ENSURE(d->ray_base, R + 1, ray_base);
   ENSURE(d->band_cnt, R, band_cnt);
   ENSURE(d->band_base, R + 1, band_base);
+  ENSURE(d->blk_tot, nblk, blk_tot);
+  ENSURE(d->blk_base, nblk + 1, blk_base);
   ENSURE(d->q_pts, qcap * 3, q_pts);
   ENSURE(d->q_code, qcap, q_code);
   ENSURE(d->q_samp, qcap, q_samp);
@@ -774,10 +840,23 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
   const int first_mode = d->precision == QSP_PREC_FP32_CORES ? DEC_FP32 : DEC_FAST;
   const float margin0 = first_mode == DEC_FAST ? d->margin0 : 0.f;
   const float margin1 = first_mode == DEC_FAST ? d->margin1 : 0.f;
-  const int cand_blocks = (int)((bandcap + tb - 1) / tb);
+  const int cand_blocks = (int)std::min<size_t>((bandcap + tb - 1) / tb, 65535u * 16u);
+  // counters: [0] in-ball samples, [1] candidates, [2] rows of the fwd+Jacobian launch (M + candidates that fit),
+  // [3] overflow flag, [4] max first-pass error (float bits), [5] candidates beyond 3/4 of the margin,
+  // [6] ticket of k_cand_count, [7] candidates that fit, [8..] rows of the first-pass phases
   CK(cudaMemsetAsync(counters, 0, (8 + GN_MAXC) * sizeof(int), st));
+  d->stats_dev = counters + 3;
+  d->stats_fresh = false;
   int* phase_cnt = counters + 8;
   const int n_phases = d->phases ? gn_num_phases(S) : 1;
+  // Small batches: the surface rows (M of them, known up front) get their own fwd+Jacobian launch on the side stream,
+  // on ceil(M / 64) SMs, while the first pass of the ray samples runs on the others; the candidate rows follow on the
+  // main stream.  Rows are independent of their tile, so the results are those of the single launch, bit for bit.
+  const int surf_tiles = (M + 63) / 64;
+  const bool conc = d->concurrent && d->fused && hp_mode == DEC_SPLIT && !d->debug && !d->timeline && M > 0 &&
+                    2 * surf_tiles <= d->num_sms;
+  const int surf_grid = (surf_tiles + 1) / 2 * 2;
+  const int first_grid_cap = conc ? std::max(2, d->pair_grid - surf_grid) : 0;
   std::vector<std::pair<const char*, cudaEvent_t>> marks;   // diagnostic timeline of the last iteration
 #define MARK(name)                                                        \
   do {                                                                    \
@@ -790,45 +869,78 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
   } while (0)
   for (int it = 0; it < prm->num_iterations; ++it) {
     MARK("start");
-    KL(k_prep, (B + 63) / 64, 64, st, state, B, S, phase_cnt, p.th, margin0, margin1);
+    KL(k_prep, (B + 63) / 64, 64, st, state, B, S, phase_cnt, counters, p.th, margin0, margin1);
     MARK("k_prep");
+    if (conc) {
+      CK(cudaEventRecord(d->ev_fork, st));
+      CK(cudaStreamWaitEvent(d->side, d->ev_fork, 0));
+      KL(k_surface_xform, std::max(1, (M + tb - 1) / tb), tb, d->side, state, in.pts, pt_obj, M, jp_pts, jp_code);
+      if ((r = launch_decoder(d, hp_mode, true, jp_pts, jp_code, codes_dev, code_stride, M, nullptr, 1, g_sdf, g_jac, d->side, nullptr, surf_grid))) return r;
+      CK(cudaEventRecord(d->ev_join, d->side));
+    }
     // (b) sample, in-ball test, ordered compaction
-    KL(k_sample<false>, ray_blocks, tb, st, state, in.rays, ray_obj, R, S, ray_cnt, nullptr, nullptr, nullptr, nullptr);
-    KL(k_exclusive_scan, 1, 1024, st, ray_cnt, ray_base, R, counters + 0, 0, nullptr);
-    KL(k_sample<true>, ray_blocks, tb, st, state, in.rays, ray_obj, R, S, nullptr, ray_base, q_pts, q_code, q_samp);
-    MARK("k_sample x2 + scan");
+    if (d->fused) {
+      KL(k_sample_fused, ray_blocks, tb, st, state, in.rays, ray_obj, R, S, ray_cnt, ray_base, counters + 0, q_pts, q_code, q_samp);
+      MARK("k_sample_fused");
+    } else {
+      KL(k_sample<false>, ray_blocks, tb, st, state, in.rays, ray_obj, R, S, ray_cnt, nullptr, nullptr, nullptr, nullptr);
+      KL(k_exclusive_scan, 1, 1024, st, ray_cnt, ray_base, R, counters + 0, 0, nullptr, INT_MAX);
+      KL(k_sample<true>, ray_blocks, tb, st, state, in.rays, ray_obj, R, S, nullptr, ray_base, q_pts, q_code, q_samp);
+      MARK("k_sample x2 + scan");
+    }
     // (a) forward decode of the in-ball samples (loss.py:77-78), first pass
     // in phases of 32 samples along the ray; a ray stops at its first certainly-opaque sample (k_phase_list)
     if (d->phases) {
       for (int ph = 0; ph < n_phases; ++ph) {
-        KL(k_phase_list, ray_blocks, tb, st, ph, (int)(ph == n_phases - 1), R, state, ray_obj, ray_base, q_sdf, q_code, ray_nev, ph_list, ph_code, phase_cnt);
+        KL(k_phase_list, ray_blocks, tb, st, ph, (int)(ph == n_phases - 1), R, state, ray_obj, ray_base, ray_cnt, q_sdf, q_code, ray_nev, ph_list, ph_code, phase_cnt);
         MARK("k_phase_list");
-        if ((r = launch_decoder(d, first_mode, false, q_pts, ph_code, codes_dev, code_stride, 0, phase_cnt + ph, 1, q_sdf, nullptr, st, ph_list))) return r;
+        if ((r = launch_decoder(d, first_mode, false, q_pts, ph_code, codes_dev, code_stride, 0, phase_cnt + ph, 1, q_sdf, nullptr, st, ph_list, first_grid_cap))) return r;
         MARK("first-pass decoder");
       }
     } else {
-      if ((r = launch_decoder(d, first_mode, false, q_pts, q_code, codes_dev, code_stride, 0, counters + 0, 1, q_sdf, nullptr, st))) return r;
+      if ((r = launch_decoder(d, first_mode, false, q_pts, q_code, codes_dev, code_stride, 0, counters + 0, 1, q_sdf, nullptr, st, nullptr, first_grid_cap))) return r;
     }
     const int* nev = d->phases ? ray_nev : ray_cnt;     // decoded samples per ray
     // candidates near the band, appended behind the surface points in the Jacobian row list
-    KL(k_candidates<false>, ray_blocks, tb, st, state, ray_obj, ray_base, nev, R, q_sdf, band_cnt, nullptr, M, (int)bandcap, nullptr,
-                                                   nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
-    KL(k_exclusive_scan, 1, 1024, st, band_cnt, band_base, R, counters + 1, M, counters + 2);
-    KL(k_candidates<true>, ray_blocks, tb, st, state, ray_obj, ray_base, nev, R, q_sdf, nullptr, band_base, M, (int)bandcap, q_pts,
-                                                  q_code, q_samp, jp_pts, jp_code, row_ray, row_samp, cand_q, counters + 3);
-    KL(k_surface_xform, std::max(1, (M + tb - 1) / tb), tb, st, state, in.pts, pt_obj, M, jp_pts, jp_code);
-    MARK("k_candidates x2 + scan + k_surface_xform");
+    if (d->fused) {
+      KL(k_cand_count, nblk, 32 * GN_RAYS_PER_BLOCK, st, state, ray_obj, ray_base, nev, R, q_sdf, band_cnt, blk_tot, blk_base,
+                                               band_base + R, counters, M, (int)bandcap);
+      KL(k_cand_fill, nblk, 32 * GN_RAYS_PER_BLOCK, st, state, ray_obj, ray_base, nev, R, q_sdf, band_cnt, blk_base, band_base, M,
+                                              (int)bandcap, q_pts, q_code, q_samp, jp_pts, jp_code, row_ray, row_samp, cand_q, counters + 3);
+    } else {
+      KL(k_candidates<false>, ray_blocks, tb, st, state, ray_obj, ray_base, nev, R, q_sdf, band_cnt, nullptr, M, (int)bandcap, nullptr,
+                                                     nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+      KL(k_exclusive_scan, 1, 1024, st, band_cnt, band_base, R, counters + 1, M, counters + 2, (int)bandcap);
+      KL(k_candidates<true>, ray_blocks, tb, st, state, ray_obj, ray_base, nev, R, q_sdf, nullptr, band_base, M, (int)bandcap, q_pts,
+                                                    q_code, q_samp, jp_pts, jp_code, row_ray, row_samp, cand_q, counters + 3);
+    }
     // (a) SDF + input Jacobian of surface points and candidates (loss.py:34,144), fp32-equivalent
-    if ((r = launch_decoder(d, hp_mode, true, jp_pts, jp_code, codes_dev, code_stride, 0, counters + 2, 1, g_sdf, g_jac, st))) return r;
+    if (conc) {
+      MARK("candidates");
+      if ((r = launch_decoder(d, hp_mode, true, jp_pts + (size_t)M * 3, jp_code + M, codes_dev, code_stride, 0, counters + 7, 1,
+                              g_sdf + M, g_jac + (size_t)M * QSP_JSTRIDE, st))) return r;
+    } else {
+      KL(k_surface_xform, std::max(1, (M + tb - 1) / tb), tb, st, state, in.pts, pt_obj, M, jp_pts, jp_code);
+      MARK("candidates + k_surface_xform");
+      if ((r = launch_decoder(d, hp_mode, true, jp_pts, jp_code, codes_dev, code_stride, 0, counters + 2, 1, g_sdf, g_jac, st))) return r;
+    }
     MARK("fwd+Jacobian decoder");
-    KL(k_refine_scatter, cand_blocks, tb, st, counters + 1, (int)bandcap, cand_q, g_sdf, M, q_sdf);
     // (b) occupancy, transmittance, rendered depth, band selection
-    KL(k_render, ray_blocks, tb, st, state, in.rays, ray_obj, d_rays_off, in.depth, d_depth_off, R, S, p.th,
-                                        ray_base, q_sdf, nev, slot, ray_res, band_cnt);
-    KL(k_row_factors, cand_blocks, tb, st, counters + 1, (int)bandcap, M, S, row_ray, row_samp, slot, ray_res,
-                                              row_fac, row_res);
-    MARK("k_refine_scatter + k_render + k_row_factors");
+    if (d->fused) {
+      RenderFused fz{band_base, cand_q, g_sdf, row_samp, row_fac, row_res, counters + 4, M, (int)bandcap};
+      KL(k_render<true>, ray_blocks, tb, st, state, in.rays, ray_obj, d_rays_off, in.depth, d_depth_off, R, S, p.th,
+                                                 ray_base, q_sdf, nev, slot, ray_res, band_cnt, fz);
+      MARK("k_render (fused)");
+    } else {
+      KL(k_refine_scatter, cand_blocks, tb, st, counters + 1, (int)bandcap, cand_q, g_sdf, M, q_sdf);
+      KL(k_render<false>, ray_blocks, tb, st, state, in.rays, ray_obj, d_rays_off, in.depth, d_depth_off, R, S, p.th,
+                                                  ray_base, q_sdf, nev, slot, ray_res, band_cnt, RenderFused{});
+      KL(k_row_factors, cand_blocks, tb, st, counters + 1, (int)bandcap, M, S, row_ray, row_samp, slot, ray_res,
+                                                row_fac, row_res);
+      MARK("k_refine_scatter + k_render + k_row_factors");
+    }
     // (c) chain rule + normal equations, (d) solve + update
+    if (conc) CK(cudaStreamWaitEvent(st, d->ev_join, 0));      // the surface rows of the side stream
     KL(k_accumulate, dim3(nchunk, B, 2), 256, st, state, d_pts_off, d_rays_off, band_base, M, jp_pts, g_sdf, g_jac,
                                                      row_fac, row_res, p.b2, p.b1, 0, nullptr, partials);
     MARK("k_accumulate");
@@ -907,15 +1019,32 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
   }
   if (host) {
     CK(cudaMemcpyAsync(records, d_rec, (size_t)B * QSP_RECORD_LEN * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(d->last_stats, counters + 3, 3 * sizeof(int), cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
+    d->stats_fresh = true;
   } else if (flags & QSP_FLAG_SYNC) {
     CK(cudaStreamSynchronize(st));
   }
-  if (host || (flags & QSP_FLAG_SYNC)) {
-    int ovf = 0;
-    CK(cudaMemcpy(&ovf, counters + 3, sizeof(int), cudaMemcpyDeviceToHost));
-    if (ovf) { g_err = "candidate row capacity exceeded"; return QSP_ERR_ALLOC; }
+  return QSP_OK;
+}
+
+// Diagnostics of the last qsp_reconstruct_batch call on this handle (synchronises the device unless that call was a
+// host-pointer call): overflow != 0 - some objects failed (is_good = 0) because their candidate rows did not fit the
+// row buffers; max_first_pass_error - the largest |fp16 first pass - fp32-equivalent| SDF seen on a candidate row;
+// n_margin_excursions - candidates whose first-pass error exceeded 3/4 of the object's margin (any > 0 means the
+// margin is too tight for this decoder: qsp_set_first_pass_margin / DeviceDecoder.calibrate_first_pass_margin).
+extern "C" int qsp_get_call_stats(qsp_decoder* d, int32_t* overflow, float* max_first_pass_error, int32_t* n_margin_excursions) {
+  if (!d) { g_err = "null handle"; return QSP_ERR_INVALID; }
+  LOCK(d);
+  if (!d->stats_fresh && d->stats_dev) {
+    CK(cudaSetDevice(d->device));
+    CK(cudaDeviceSynchronize());
+    CK(cudaMemcpy(d->last_stats, d->stats_dev, 3 * sizeof(int), cudaMemcpyDeviceToHost));
+    d->stats_fresh = true;
   }
+  if (overflow) *overflow = d->last_stats[0];
+  if (max_first_pass_error) memcpy(max_first_pass_error, &d->last_stats[1], sizeof(float));
+  if (n_margin_excursions) *n_margin_excursions = d->last_stats[2];
   return QSP_OK;
 }
 
@@ -1103,6 +1232,7 @@ extern "C" int qsp_estimate_pose_batch(qsp_decoder* d, int32_t num_iterations, i
   }
   int r;
   if ((r = check_offsets(pts_off, B, "pts"))) return r;
+  LOCK(d);
   CK(cudaSetDevice(d->device));
   cudaStream_t st = (cudaStream_t)stream;
   const bool host = flags & QSP_FLAG_HOST_PTRS;
@@ -1190,7 +1320,7 @@ static int pool_ready(int device) {
 static int scan_ints(const int* in, int* out, long n, int* seg_tmp, cudaStream_t st) {
   const int nseg = (int)((n + SCAN_SEG - 1) / SCAN_SEG);
   k_scan_segments<<<nseg, SCAN_SEG, 0, st>>>(in, out, (int)n, seg_tmp); LAUNCHED();
-  k_exclusive_scan<<<1, 1024, 0, st>>>(seg_tmp, seg_tmp + nseg, nseg, nullptr, 0, nullptr); LAUNCHED();
+  k_exclusive_scan<<<1, 1024, 0, st>>>(seg_tmp, seg_tmp + nseg, nseg, nullptr, 0, nullptr, INT_MAX); LAUNCHED();
   k_scan_add<<<nseg, SCAN_SEG, 0, st>>>(out, (int)n, seg_tmp + nseg, nseg); LAUNCHED();
   return QSP_OK;
 }
@@ -1260,6 +1390,7 @@ extern "C" int qsp_mesh_extract(const float* sdf, int32_t D, float level, float 
 
 extern "C" int qsp_set_voxel_grid(qsp_decoder* d, const float* pts, int32_t D, uint32_t flags, void* stream) {
   if (!d || !pts || D < 2 || D > 1024) { g_err = "bad argument"; return QSP_ERR_INVALID; }
+  LOCK(d);
   CK(cudaSetDevice(d->device));
   cudaStream_t st = (cudaStream_t)stream;
   const size_t V = (size_t)D * D * D;
@@ -1274,6 +1405,7 @@ extern "C" int qsp_set_voxel_grid(qsp_decoder* d, const float* pts, int32_t D, u
 extern "C" int qsp_extract_mesh(qsp_decoder* d, const float* code, float level, float spacing, const float* origin,
                                 float* sdf_out, uint32_t flags, void* stream, qsp_mesh** out) {
   if (!d || !code || !origin || !out) { g_err = "bad argument"; return QSP_ERR_INVALID; }
+  LOCK(d);
   if (d->grid_D < 2) { g_err = "qsp_set_voxel_grid has not been called"; return QSP_ERR_INVALID; }
   CK(cudaSetDevice(d->device));
   cudaStream_t st = (cudaStream_t)stream;

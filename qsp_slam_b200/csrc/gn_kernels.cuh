@@ -101,10 +101,11 @@ __device__ inline void rotation_prior_dev(const float* T_co, float scale, float*
 
 // depth range, background depth and rotation prior of the current pose (optimizer.py:144-153,
 // loss.py:155-178)
-__global__ void k_prep(ObjState* st, int B, int S, int* phase_cnt, float th, float margin0, float margin_per_norm) {
+__global__ void k_prep(ObjState* st, int B, int S, int* phase_cnt, int* counters, float th, float margin0, float margin_per_norm) {
   pdl_prologue();
   int o = blockIdx.x * blockDim.x + threadIdx.x;
   if (phase_cnt && o < GN_MAXC) phase_cnt[o] = 0;      // row counts of this iteration's first-pass phases
+  if (counters && o == 0) counters[0] = 0;             // in-ball samples of this iteration (k_sample_fused reserves ranges)
   if (o >= B) return;
   ObjState& s = st[o];
   if (s.failed) return;
@@ -113,6 +114,9 @@ __global__ void k_prep(ObjState* st, int B, int S, int* phase_cnt, float th, flo
   double det = (double)C[0] * ((double)C[5] * C[10] - (double)C[6] * C[9]) -
                (double)C[1] * ((double)C[4] * C[10] - (double)C[6] * C[8]) +
                (double)C[2] * ((double)C[4] * C[9] - (double)C[5] * C[8]);
+  // torch: det ** (1/3) is NaN for a negative determinant -> NaN depth range -> no in-ball sample -> is_good = False
+  // (optimizer.py:148-151, loss.py:73-74); same outcome here
+  if (!(det > 0.0)) { s.failed = 1; return; }
   float scale = cbrtf((float)det);
   s.scale = scale;
   s.d_min = __fsub_rn(s.T_co[11], scale);
@@ -192,6 +196,60 @@ __global__ void k_sample(const ObjState* __restrict__ st, const float* __restric
   if (!FILL && lane == 0) ray_cnt[r] = cnt;
 }
 
+// One-pass form of the two k_sample launches and the scan between them: the warp counts its ray's in-ball samples,
+// reserves a contiguous range of the sample list with ONE atomicAdd and fills it.  The order of the RAYS in the list
+// is then arbitrary - nothing depends on it: every consumer (k_phase_list, k_candidates, k_render) addresses a ray's
+// samples through ray_base[r] / ray_cnt[r], and the candidate rows get their (ray, sample) order from their own scan.
+__global__ void k_sample_fused(const ObjState* __restrict__ st, const float* __restrict__ rays,
+                               const int* __restrict__ ray_obj, int R, int S, int* __restrict__ ray_cnt,
+                               int* __restrict__ ray_base, int* __restrict__ total, float* __restrict__ q_pts,
+                               int* __restrict__ q_code, int* __restrict__ q_samp) {
+  pdl_prologue();
+  int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (r >= R) return;
+  int o = ray_obj[r];
+  if (st[o].failed) {
+    if (lane == 0) { ray_cnt[r] = 0; ray_base[r] = 0; }
+    return;
+  }
+  RayCtx c = load_ray(st, o, rays, r);
+  const int nc = (S + 31) >> 5;
+  float px[GN_MAXC], py[GN_MAXC], pz[GN_MAXC];
+  unsigned msk[GN_MAXC];
+  int cnt = 0;
+#pragma unroll
+  for (int ch = 0; ch < GN_MAXC; ++ch) {
+    msk[ch] = 0u; px[ch] = py[ch] = pz[ch] = 0.f;
+    if (ch < nc) {
+      int j = ch * 32 + lane;
+      bool in = false;
+      if (j < S) {
+        sample_point(c.T, c.rx, c.ry, c.rz, linspace_at(c.d_min, c.d_max, c.step, j, S), px[ch], py[ch], pz[ch]);
+        in = in_ball(px[ch], py[ch], pz[ch]);
+      }
+      msk[ch] = __ballot_sync(0xffffffffu, in);
+      cnt += __popc(msk[ch]);
+    }
+  }
+  int base = 0;
+  if (lane == 0 && cnt > 0) base = atomicAdd(total, cnt);
+  base = __shfl_sync(0xffffffffu, base, 0);
+  int run = base;
+#pragma unroll
+  for (int ch = 0; ch < GN_MAXC; ++ch) {
+    if (ch < nc) {
+      if ((msk[ch] >> lane) & 1u) {
+        int idx = run + __popc(msk[ch] & ((1u << lane) - 1u));
+        q_pts[idx * 3 + 0] = px[ch]; q_pts[idx * 3 + 1] = py[ch]; q_pts[idx * 3 + 2] = pz[ch];
+        q_code[idx] = o;
+        q_samp[idx] = ch * 32 + lane;
+      }
+      run += __popc(msk[ch]);
+    }
+  }
+  if (lane == 0) { ray_cnt[r] = cnt; ray_base[r] = base; }
+}
+
 // First pass in phases along the ray (front to back).  Phase p decodes in-ball samples [32p, 32p + 32) (the last
 // phase: up to 32 + GN_PHASE_TAIL) of every
 // ray that has not met a certainly-opaque sample (first-pass s <= -lim, hence exact s <= -th and occupancy exactly
@@ -207,13 +265,13 @@ __host__ __device__ inline int gn_num_phases(int S) {
   return (full > 1 && rem <= GN_PHASE_TAIL) ? full - 1 : full;
 }
 __global__ void k_phase_list(int p, int last, int R, const ObjState* __restrict__ st, const int* __restrict__ ray_obj,
-                             const int* __restrict__ ray_base, const float* __restrict__ q_sdf,
+                             const int* __restrict__ ray_base, const int* __restrict__ ray_cnt, const float* __restrict__ q_sdf,
                              const int* __restrict__ q_code, int* __restrict__ ray_nev,
                              int* __restrict__ list, int* __restrict__ list_code, int* __restrict__ phase_cnt) {
   pdl_prologue();
   int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (r >= R) return;
-  const int lo = ray_base[r], n = ray_base[r + 1] - lo, start = p * 32;
+  const int lo = ray_base[r], n = ray_cnt[r], start = p * 32;
   if (p == 0 && lane == 0) ray_nev[r] = 0;
   if (start >= n) return;
   if (p > 0) {
@@ -237,9 +295,9 @@ __global__ void k_phase_list(int p, int last, int R, const ObjState* __restrict_
 // elements (all its loads in flight together), so 1024 threads cover 8192 elements per pass with one block-wide
 // scan of the thread sums: one pass for a 32-object frame (8192 rays), three barriers per pass.
 #define SCAN_ITEMS 8
-__global__ void k_exclusive_scan(const int* __restrict__ in, int* __restrict__ out, int n,
-                                 int* total, int total_add, int* total2) {
-  pdl_prologue();
+// exclusive scan of in[0..n) into out[0..n) by ONE thread block (any blockDim.x that is a multiple of 32); returns the
+// total to every thread.  Loads bypass L1 (__ldcg): the fused callers scan values other blocks have just written.
+__device__ inline int block_exclusive_scan(const int* __restrict__ in, int* __restrict__ out, int n) {
   __shared__ int wsum[32];
   __shared__ int carry_s;
   const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
@@ -249,7 +307,7 @@ __global__ void k_exclusive_scan(const int* __restrict__ in, int* __restrict__ o
     const int i0 = base + tid * SCAN_ITEMS;
     int v[SCAN_ITEMS];
 #pragma unroll
-    for (int k = 0; k < SCAN_ITEMS; ++k) v[k] = i0 + k < n ? in[i0 + k] : 0;
+    for (int k = 0; k < SCAN_ITEMS; ++k) v[k] = i0 + k < n ? __ldcg(in + i0 + k) : 0;
     int mine = 0;
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS; ++k) mine += v[k];
@@ -280,10 +338,20 @@ __global__ void k_exclusive_scan(const int* __restrict__ in, int* __restrict__ o
     if (tid == blockDim.x - 1) carry_s = run;
   }
   __syncthreads();
-  if (tid == 0) {
-    out[n] = carry_s;
-    if (total) *total = carry_s;
-    if (total2) *total2 = carry_s + total_add;
+  return carry_s;
+}
+
+// exclusive scan of n ints into out[0..n] (out[n] = total); single block.  A thread owns SCAN_ITEMS consecutive
+// elements (all its loads in flight together), so 1024 threads cover 8192 elements per pass with one block-wide
+// scan of the thread sums: one pass for a 32-object frame (8192 rays), three barriers per pass.
+__global__ void k_exclusive_scan(const int* __restrict__ in, int* __restrict__ out, int n,
+                                 int* total, int total_add, int* total2, int cap) {
+  pdl_prologue();
+  const int tot = block_exclusive_scan(in, out, n);
+  if (threadIdx.x == 0) {
+    out[n] = tot;
+    if (total) *total = tot;
+    if (total2) *total2 = min(tot, cap) + total_add;   // rows the fwd+Jacobian launch evaluates: never beyond the buffers
   }
 }
 
@@ -292,19 +360,60 @@ __global__ void k_exclusive_scan(const int* __restrict__ in, int* __restrict__ o
 // (loss.py:84-141).  One warp per ray.  Writes, per ray: the clamped depth residual and the number
 // of kept band samples; per (ray, sample) slot: de_ds of kept samples, 0 elsewhere.
 // ------------------------------------------------------------------------------------------------
+// FUSED: the warp first writes the exact SDF of its ray's candidate rows into the sample list (k_refine_scatter),
+// keeping track of how far the first pass was off, and at the end fills the rows' factor and residual
+// (k_row_factors); band_cnt is not written (only the unfused k_band_fill path reads it).
+struct RenderFused {
+  const int* band_base;     // [R+1] candidate row range of every ray
+  const int* cand_q;        // candidate k -> index into the sample list
+  const float* g_sdf;       // exact SDF of row row0 + k
+  const int* row_samp;      // sample index of row row0 + k
+  float* row_fac;
+  float* row_res;
+  int* stats;               // [0] max |first pass - exact| (float bits), [1] candidates beyond 3/4 of the margin
+  int row0, cap;
+};
+template <bool FUSED>
 __global__ void k_render(ObjState* __restrict__ st, const float* __restrict__ rays,
                          const int* __restrict__ ray_obj, const int* __restrict__ rays_off,
                          const float* __restrict__ depth, const int* __restrict__ depth_off,
                          int R, int S, float th, const int* __restrict__ ray_base,
-                         const float* __restrict__ q_sdf, const int* __restrict__ ray_nev,
-                         float* __restrict__ slot_de_ds, float* __restrict__ ray_res, int* __restrict__ band_cnt) {
+                         float* __restrict__ q_sdf, const int* __restrict__ ray_nev,
+                         float* __restrict__ slot_de_ds, float* __restrict__ ray_res, int* __restrict__ band_cnt,
+                         RenderFused fz) {
   pdl_prologue();
   int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (r >= R) return;
   int o = ray_obj[r];
   if (st[o].failed) {
-    if (lane == 0) band_cnt[r] = 0;
+    if (!FUSED && lane == 0) band_cnt[r] = 0;
     return;
+  }
+  int cb = 0, ce = 0;
+  if (FUSED) {
+    cb = min(fz.band_base[r], fz.cap); ce = min(fz.band_base[r + 1], fz.cap);
+    const float lim34 = 0.75f * (st[o].cand_lim - th);
+    float emax = 0.f;
+    int nexc = 0;
+    for (int k = cb + lane; k < ce; k += 32) {
+      const int qi = fz.cand_q[k];
+      const float exact = fz.g_sdf[fz.row0 + k], err = fabsf(q_sdf[qi] - exact);
+      q_sdf[qi] = exact;
+      emax = fmaxf(emax, err);
+      nexc += err > lim34;
+    }
+    if (ce > cb) {
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) {
+        emax = fmaxf(emax, __shfl_xor_sync(0xffffffffu, emax, d));
+        nexc += __shfl_xor_sync(0xffffffffu, nexc, d);
+      }
+      if (lane == 0) {
+        if (emax > 0.f) atomicMax(fz.stats, __float_as_int(emax));     // non-negative floats order like ints
+        if (nexc) atomicAdd(fz.stats + 1, nexc);
+      }
+    }
+    __syncwarp();                                        // the lanes read each other's q_sdf entries below
   }
   RayCtx c = load_ray(st, o, rays, r);
   const int nc = (S + 31) >> 5;
@@ -388,11 +497,19 @@ __global__ void k_render(ObjState* __restrict__ st, const float* __restrict__ ra
     }
   }
   if (lane == 0) {
-    band_cnt[r] = kept;
+    if (!FUSED) band_cnt[r] = kept;
     ray_res[r] = res;
     atomicAdd(&st[o].n_inball, cnt);
     atomicAdd(&st[o].n_band, nband);
     atomicAdd(&st[o].n_keep, kept);
+  }
+  if (FUSED && ce > cb) {
+    __syncwarp();                                        // this ray's slots were written by the other lanes
+    for (int k = cb + lane; k < ce; k += 32) {
+      const int row = fz.row0 + k;
+      fz.row_fac[row] = slot_de_ds[(size_t)r * S + fz.row_samp[row]];
+      fz.row_res[row] = res;
+    }
   }
 }
 
@@ -959,7 +1076,10 @@ __global__ void k_finalize_pose_only(const ObjState* __restrict__ st, const floa
   inv_affine(st[o].T_oc, T);
   for (int r = 0; r < 3; ++r)
     for (int c = 0; c < 3; ++c) T[r * 4 + c] /= scale[o];
-  for (int i = 0; i < 16; ++i) out[o * 16 + i] = T[i];
+  // every surface point pruned at iteration 4 (optimizer.py:80-82): the reference's 0-row mean is NaN and so is the
+  // pose it returns (:72-76, :87-88)
+  const float nanv = __int_as_float(0x7fc00000);
+  for (int i = 0; i < 16; ++i) out[o * 16 + i] = st[o].failed ? nanv : T[i];
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -971,7 +1091,7 @@ __global__ void k_finalize_pose_only(const ObjState* __restrict__ st, const floa
 // Order: (ray, sample) ascending, i.e. the order torch.where gives (loss.py:68,89-90).
 // ------------------------------------------------------------------------------------------------
 template <bool FILL>
-__global__ void k_candidates(const ObjState* __restrict__ st, const int* __restrict__ ray_obj,
+__global__ void k_candidates(ObjState* __restrict__ st, const int* __restrict__ ray_obj,
                              const int* __restrict__ ray_base, const int* __restrict__ ray_nev, int R,
                              const float* __restrict__ q_sdf, int* __restrict__ cand_cnt, const int* __restrict__ cand_base,
                              int row0, int cap, const float* __restrict__ q_pts, const int* __restrict__ q_code,
@@ -1005,6 +1125,9 @@ __global__ void k_candidates(const ObjState* __restrict__ st, const int* __restr
         row_samp[row] = q_samp[i];
         cand_q[k] = i;
       } else {
+        // no room for this row: the OBJECT fails (is_good = 0) instead of the call; nothing is read or written
+        // beyond the row buffers (k_accumulate / k_solve skip failed objects)
+        st[ray_obj[r]].failed = 2;
         *overflow = 1;
       }
     }
@@ -1012,6 +1135,106 @@ __global__ void k_candidates(const ObjState* __restrict__ st, const int* __restr
     if (mo) break;
   }
   if (!FILL && lane == 0) cand_cnt[r] = cnt;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Fused forms of the launches around the fwd+Jacobian decoder (same arithmetic, same row order, fewer launches):
+//   k_cand_count   = k_candidates<count> + the scan: blocks of 8 rays write their totals; the LAST block to finish
+//                    (ticket) scans the block totals - 8x fewer entries than rays, so one block covers a map-scale call
+//   k_cand_fill    = k_candidates<fill>, each block re-deriving its rays' offsets from the block base
+//   k_render_fused = k_refine_scatter + k_render + k_row_factors: a ray's candidates, samples and rows belong to
+//                    the warp that renders the ray
+// ------------------------------------------------------------------------------------------------
+#define GN_RAYS_PER_BLOCK 8
+// candidates of one ray (the logic of k_candidates): calls f(i, k) for the k-th candidate, in-ball sample index i
+template <class F>
+__device__ __forceinline__ int for_each_candidate(int lo, int hi, float lim, const float* __restrict__ q_sdf, int lane, F f) {
+  int cnt = 0;
+  for (int i0 = lo; i0 < hi; i0 += 32) {
+    const int i = i0 + lane;
+    bool c = false, opq = false;
+    if (i < hi) { const float s = q_sdf[i]; c = (s > -lim) && (s < lim); opq = s <= -lim; }
+    const unsigned mo = __ballot_sync(0xffffffffu, opq);
+    if (mo) c = c && lane < __ffs(mo) - 1;                // nothing behind the first certainly-opaque sample
+    const unsigned m = __ballot_sync(0xffffffffu, c);
+    if (c) f(i, cnt + __popc(m & ((1u << lane) - 1u)));
+    cnt += __popc(m);
+    if (mo) break;
+  }
+  return cnt;
+}
+
+__global__ void __launch_bounds__(32 * GN_RAYS_PER_BLOCK)
+k_cand_count(const ObjState* __restrict__ st, const int* __restrict__ ray_obj, const int* __restrict__ ray_base,
+             const int* __restrict__ ray_nev, int R, const float* __restrict__ q_sdf, int* __restrict__ cand_cnt,
+             int* __restrict__ blk_tot, int* __restrict__ blk_base, int* __restrict__ band_base_end,
+             int* __restrict__ counters, int M, int cap) {
+  pdl_prologue();
+  __shared__ int s_cnt[GN_RAYS_PER_BLOCK];
+  __shared__ int s_last;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int r = blockIdx.x * GN_RAYS_PER_BLOCK + warp;
+  int cnt = 0;
+  if (r < R) {
+    const int lo = ray_base[r];
+    cnt = for_each_candidate(lo, lo + ray_nev[r], st[ray_obj[r]].cand_lim, q_sdf, lane, [](int, int) {});
+    if (lane == 0) cand_cnt[r] = cnt;
+  }
+  if (lane == 0) s_cnt[warp] = cnt;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int t = 0;
+#pragma unroll
+    for (int w = 0; w < GN_RAYS_PER_BLOCK; ++w) t += s_cnt[w];
+    blk_tot[blockIdx.x] = t;
+    __threadfence();
+    s_last = atomicAdd(counters + 6, 1) == (int)gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const int tot = block_exclusive_scan(blk_tot, blk_base, (int)gridDim.x);
+  if (threadIdx.x == 0) {
+    *band_base_end = tot;                                 // band_base[R]
+    counters[1] = tot;
+    counters[2] = M + min(tot, cap);                      // rows of the fwd+Jacobian launch
+    counters[7] = min(tot, cap);                          // candidate rows alone (their own launch in small batches)
+    counters[6] = 0;                                      // ticket for the next launch
+  }
+}
+
+__global__ void __launch_bounds__(32 * GN_RAYS_PER_BLOCK)
+k_cand_fill(ObjState* __restrict__ st, const int* __restrict__ ray_obj, const int* __restrict__ ray_base,
+            const int* __restrict__ ray_nev, int R, const float* __restrict__ q_sdf, const int* __restrict__ cand_cnt,
+            const int* __restrict__ blk_base, int* __restrict__ band_base, int row0, int cap,
+            const float* __restrict__ q_pts, const int* __restrict__ q_code, const int* __restrict__ q_samp,
+            float* __restrict__ jp_pts, int* __restrict__ jp_code, int* __restrict__ row_ray, int* __restrict__ row_samp,
+            int* __restrict__ cand_q, int* __restrict__ overflow) {
+  pdl_prologue();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int r = blockIdx.x * GN_RAYS_PER_BLOCK + warp;
+  if (r >= R) return;
+  int base = blk_base[blockIdx.x];
+  for (int w = 0; w < warp; ++w) base += cand_cnt[blockIdx.x * GN_RAYS_PER_BLOCK + w];
+  const int mine = cand_cnt[r];
+  if (lane == 0) band_base[r] = base;
+  if (mine == 0) return;
+  const int o = ray_obj[r];
+  if (base + mine > cap) {                                // see k_candidates: the object fails, not the call
+    if (lane == 0) { st[o].failed = 2; *overflow = 1; }
+  }
+  const int lo = ray_base[r];
+  for_each_candidate(lo, lo + ray_nev[r], st[o].cand_lim, q_sdf, lane, [&](int i, int kk) {
+    const int k = base + kk;
+    if (k < cap) {
+      const int row = row0 + k;
+      jp_pts[row * 3] = q_pts[i * 3]; jp_pts[row * 3 + 1] = q_pts[i * 3 + 1]; jp_pts[row * 3 + 2] = q_pts[i * 3 + 2];
+      jp_code[row] = q_code[i];
+      row_ray[row] = r;
+      row_samp[row] = q_samp[i];
+      cand_q[k] = i;
+    }
+  });
 }
 
 // exact SDF of the candidates back into the per-sample list read by k_render

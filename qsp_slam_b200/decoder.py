@@ -8,6 +8,7 @@ on one GPU.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Dict, Optional
 
 import numpy as np
@@ -35,7 +36,10 @@ class DeviceDecoder:
     """Owns a ``qsp_decoder*``.  ``decoder`` may be a state dict, an ``nn.Module`` or another
     ``DeviceDecoder`` (returned as is by :func:`as_device_decoder`)."""
 
-    def __init__(self, decoder, device: int = 0):
+    def __init__(self, decoder, device: int = 0, calibrate: Optional[bool] = None):
+        """``calibrate`` (default: on, ``QSP_CALIBRATE=0`` turns it off): measure the fp16 first-pass error on THESE
+        weights and raise the candidate margin if the defaults - measured on random-init decoders - do not cover it
+        (:meth:`calibrate_first_pass_margin`; ~50 ms, a few decoder launches)."""
         st = _to_numpy_state(decoder)
         for l in range(8):
             for key, shape in ((f"lin{l}.weight_v", (_OUT[l], _IN[l])), (f"lin{l}.weight_g", (_OUT[l], 1)),
@@ -56,14 +60,20 @@ class DeviceDecoder:
         w.lin8_weight = st["lin8.weight"].ctypes.data_as(fp)
         w.lin8_bias = st["lin8.bias"].ctypes.data_as(fp)
         h = C.c_void_p()
-        N.check(N.lib().qsp_decoder_create(C.byref(w), int(device), C.byref(h)))
+        self._L = N.lib()                     # the library build this handle belongs to (tests may bind another one)
+        N.check(self._L.qsp_decoder_create(C.byref(w), int(device), C.byref(h)))
         self.handle = h
         self.device = int(device)
         self.state = st
+        self.margin_calibration = None
+        if calibrate is None:
+            calibrate = os.environ.get("QSP_CALIBRATE", "1") != "0"
+        if calibrate:
+            self.margin_calibration = self.calibrate_first_pass_margin(n_points=131072, codes_per_norm=2)
 
     def close(self):
         if getattr(self, "handle", None):
-            N.lib().qsp_decoder_destroy(self.handle)
+            self._L.qsp_decoder_destroy(self.handle)
             self.handle = None
 
     def __del__(self):
@@ -83,13 +93,13 @@ class DeviceDecoder:
     def set_precision(self, precision: str):
         """Arithmetic of the decoder inside the GN loop: "tensor" (tcgen05, fp16-pair operands, default)
         or "fp32" (exact-fp32 CUDA-core kernel, for validation)."""
-        N.check(N.lib().qsp_set_precision(self.handle, {"tensor": N.PREC_TENSOR, "fp32": N.PREC_FP32_CORES}[precision]))
+        N.check(self._L.qsp_set_precision(self.handle, {"tensor": N.PREC_TENSOR, "fp32": N.PREC_FP32_CORES}[precision]))
 
     def set_first_pass_margin(self, margin0: float = 0.0045, margin_per_norm: float = 0.004):
         """Samples whose fp16 first-pass |sdf| is below cut_off + margin0 + margin_per_norm * |code| are re-evaluated
         with fp32-equivalent arithmetic (GN loop and mesh extraction); results are exact while the first-pass error
         stays below the margin."""
-        N.check(N.lib().qsp_set_first_pass_margin(self.handle, float(margin0), float(margin_per_norm)))
+        N.check(self._L.qsp_set_first_pass_margin(self.handle, float(margin0), float(margin_per_norm)))
 
     def calibrate_first_pass_margin(self, code_norms=(0.0, 0.4, 0.8, 1.6, 2.4), n_points: int = 262144, codes_per_norm: int = 4,
                                     safety: float = 1.5, seed: int = 0, allow_lower: bool = False) -> dict:
@@ -120,12 +130,20 @@ class DeviceDecoder:
         self.set_first_pass_margin(m0, m1)
         return dict(max_error_by_code_norm=err, margin0=m0, margin_per_norm=m1)
 
+    def call_stats(self) -> dict:
+        """Diagnostics of the last GN call on this handle (``qsp_get_call_stats``): ``overflow`` (objects failed for
+        lack of candidate-row capacity), ``max_first_pass_error`` and ``n_margin_excursions`` (re-evaluated samples
+        whose fp16 first-pass error exceeded 3/4 of the margin)."""
+        ov, ex, er = C.c_int32(), C.c_int32(), C.c_float()
+        N.check(self._L.qsp_get_call_stats(self.handle, C.byref(ov), C.byref(er), C.byref(ex)))
+        return dict(overflow=int(ov.value), max_first_pass_error=float(er.value), n_margin_excursions=int(ex.value))
+
     def check_guards(self) -> int:
         """Debug (QSP_GUARD=1 in the environment): number of workspace buffers whose canary bands were overwritten
         since they were allocated, -1 if none is guarded; raises with the buffer names if any was."""
-        n = N.lib().qsp_check_guards(self.handle)
+        n = self._L.qsp_check_guards(self.handle)
         if n > 0:
-            raise N.NativeError(N.lib().qsp_last_error().decode())
+            raise N.NativeError(self._L.qsp_last_error().decode())
         return n
 
     def decode_sdf(self, codes, pts, mode: str = "tensor") -> np.ndarray:
@@ -138,7 +156,7 @@ class DeviceDecoder:
         pts = np.ascontiguousarray(pts)
         out = np.empty((codes.shape[0], pts.shape[0]), np.float32)
         if pts.shape[0]:
-            N.check(N.lib().qsp_decode_sdf(self.handle, N.ptr(codes), codes.shape[0], N.ptr(pts), pts.shape[0],
+            N.check(self._L.qsp_decode_sdf(self.handle, N.ptr(codes), codes.shape[0], N.ptr(pts), pts.shape[0],
                                            N.ptr(out), N.FLAG_HOST_PTRS | N.MODE_FLAGS[mode], None))
         return out[0] if single else out
 
@@ -146,7 +164,7 @@ class DeviceDecoder:
         """Same with torch CUDA tensors (float32, contiguous); ``out`` (C,n) is written in place."""
         n_codes = codes.numel() // 64
         n = pts.shape[0]
-        N.check(N.lib().qsp_decode_sdf(self.handle, N.ptr(codes), n_codes, N.ptr(pts), n, N.ptr(out),
+        N.check(self._L.qsp_decode_sdf(self.handle, N.ptr(codes), n_codes, N.ptr(pts), n, N.ptr(out),
                                        (N.FLAG_SYNC if sync else 0) | N.MODE_FLAGS[mode], None))
         return out
 
@@ -158,17 +176,17 @@ class DeviceDecoder:
         sdf = np.empty(n, np.float32)
         jac = np.empty((n, N.JAC_STRIDE), np.float32)
         if n:
-            N.check(N.lib().qsp_decode_sdf_jacobian(self.handle, N.ptr(code), N.ptr(pts), n, N.ptr(sdf), N.ptr(jac),
+            N.check(self._L.qsp_decode_sdf_jacobian(self.handle, N.ptr(code), N.ptr(pts), n, N.ptr(sdf), N.ptr(jac),
                                                     N.FLAG_HOST_PTRS | N.MODE_FLAGS[mode], None))
         return sdf, jac[:, :67]
 
     def decode_sdf_jacobian_device(self, code, pts, sdf, jac, sync: bool = True, mode: str = "tensor"):
-        N.check(N.lib().qsp_decode_sdf_jacobian(self.handle, N.ptr(code), N.ptr(pts), pts.shape[0], N.ptr(sdf),
+        N.check(self._L.qsp_decode_sdf_jacobian(self.handle, N.ptr(code), N.ptr(pts), pts.shape[0], N.ptr(sdf),
                                                 N.ptr(jac), (N.FLAG_SYNC if sync else 0) | N.MODE_FLAGS[mode], None))
 
     def last_kernel_ms(self) -> float:
         ms = C.c_float()
-        N.check(N.lib().qsp_kernel_ms(self.handle, C.byref(ms)))
+        N.check(self._L.qsp_kernel_ms(self.handle, C.byref(ms)))
         return float(ms.value)
 
 

@@ -15,6 +15,7 @@ from __future__ import annotations
 
 import ctypes as C
 import math
+import warnings
 from typing import List, Optional, Sequence
 
 import numpy as np
@@ -105,10 +106,30 @@ class Optimizer(object):
             z = np.ascontiguousarray(z, np.float32)
         rec = np.empty((B, N.RECORD_LEN), np.float32)
         prm = self._params()
-        N.check(N.lib().qsp_reconstruct_batch(self.decoder.handle, C.byref(prm), B, N.ptr(T), N.ptr(z),
+        N.check(self.decoder._L.qsp_reconstruct_batch(self.decoder.handle, C.byref(prm), B, N.ptr(T), N.ptr(z),
                                               N.ptr(pts), N.i32p(pts_off), N.ptr(rays), N.i32p(rays_off),
                                               N.ptr(depth), N.i32p(depth_off), N.ptr(rec), N.FLAG_HOST_PTRS, None))
+        self._check_call_stats()
         return rec
+
+    def _check_call_stats(self):
+        """Never raises (an exception would terminate the embedding SLAM process): a too-tight first-pass
+        margin or exhausted candidate-row capacity is reported once per decoder as a warning; the affected objects
+        of a capacity overflow already carry is_good = False."""
+        try:
+            st = self.decoder.call_stats()
+        except Exception:
+            return
+        self.last_call_stats = st
+        if st["n_margin_excursions"] > 0 and not getattr(self.decoder, "_warned_margin", False):
+            self.decoder._warned_margin = True
+            warnings.warn(f"qsp_slam_b200: the fp16 first pass was off by up to {st['max_first_pass_error']:.2e} on "
+                          f"{st['n_margin_excursions']} re-evaluated samples (> 3/4 of the candidate margin): band samples "
+                          "may be missed; call DeviceDecoder.calibrate_first_pass_margin() for this decoder", RuntimeWarning)
+        if st["overflow"] and not getattr(self.decoder, "_warned_overflow", False):
+            self.decoder._warned_overflow = True
+            warnings.warn("qsp_slam_b200: candidate-row capacity exceeded; the objects that did not fit were returned "
+                          "with is_good=False", RuntimeWarning)
 
     def pack(self, detections: Sequence[dict]):
         """Concatenated arrays + offsets of a detection list (the layout the C ABI takes)."""
@@ -125,7 +146,7 @@ class Optimizer(object):
         T/pts/rays/depth and host int32 numpy offsets; ``records`` (B,82) CUDA tensor is written."""
         B = packed["T"].shape[0]
         prm = self._params()
-        N.check(N.lib().qsp_reconstruct_batch(self.decoder.handle, C.byref(prm), B, N.ptr(packed["T"]), N.ptr(codes),
+        N.check(self.decoder._L.qsp_reconstruct_batch(self.decoder.handle, C.byref(prm), B, N.ptr(packed["T"]), N.ptr(codes),
                                               N.ptr(packed["pts"]), N.i32p(packed["pts_off"]), N.ptr(packed["rays"]),
                                               N.i32p(packed["rays_off"]), N.ptr(packed["depth"]),
                                               N.i32p(packed["depth_off"]), N.ptr(records),
@@ -189,25 +210,25 @@ class Optimizer(object):
         z = np.ascontiguousarray(np.stack([N.f32(c).reshape(-1)[:64] for c in codes]), np.float32)
         pts, pts_off = self._pack([N.f32(p) for p in pts_list], 3)
         out = np.empty((B, 16), np.float32)
-        N.check(N.lib().qsp_estimate_pose_batch(self.decoder.handle, int(self.num_iterations_pose_only), B, N.ptr(T),
+        N.check(self.decoder._L.qsp_estimate_pose_batch(self.decoder.handle, int(self.num_iterations_pose_only), B, N.ptr(T),
                                                 N.ptr(sc), N.ptr(z), N.ptr(pts), N.i32p(pts_off), N.ptr(out),
                                                 N.FLAG_HOST_PTRS, None))
         return [out[i].reshape(4, 4).copy() for i in range(B)]
 
     # ---- inspection for the parity tests --------------------------------------------------------
     def set_debug(self, on: bool):
-        N.check(N.lib().qsp_set_debug(self.decoder.handle, 1 if on else 0))
+        N.check(self.decoder._L.qsp_set_debug(self.decoder.handle, 1 if on else 0))
 
     def get_iteration(self, iteration: int, b: int = 0):
         H = np.empty((71, 71), np.float32)
         bv = np.empty(71, np.float32)
         dx = np.empty(71, np.float32)
         cnt = np.empty(6, np.int32)
-        N.check(N.lib().qsp_get_iteration(self.decoder.handle, iteration, b, N.ptr(H), N.ptr(bv), N.ptr(dx), N.ptr(cnt)))
+        N.check(self.decoder._L.qsp_get_iteration(self.decoder.handle, iteration, b, N.ptr(H), N.ptr(bv), N.ptr(dx), N.ptr(cnt)))
         ray = np.empty(max(int(cnt[2]), 1), np.int32)
         smp = np.empty(max(int(cnt[2]), 1), np.int32)
-        n = N.check(N.lib().qsp_get_band_indices(self.decoder.handle, iteration, b, N.ptr(ray), N.ptr(smp), ray.size))
-        n_cand = N.check(N.lib().qsp_get_band_indices(self.decoder.handle, iteration, b, None, None, -1))
+        n = N.check(self.decoder._L.qsp_get_band_indices(self.decoder.handle, iteration, b, N.ptr(ray), N.ptr(smp), ray.size))
+        n_cand = N.check(self.decoder._L.qsp_get_band_indices(self.decoder.handle, iteration, b, None, None, -1))
         return dict(H=H, b=bv, dx=dx, n_inball=int(cnt[0]), n_band=int(cnt[1]), n_keep=int(cnt[2]),
                     failed=bool(cnt[3]), keep_ray=ray[:n], keep_sample=smp[:n], n_cand=n_cand,
                     n_first_pass=int(cnt[4]))
@@ -228,7 +249,7 @@ class MeshExtractor(object):
         tag = (id(self), self.voxels_dim)
         if getattr(self.decoder, "_voxel_grid_tag", None) != tag:
             pts = np.ascontiguousarray(N.f32(self.voxel_points)[:, :3])
-            N.check(N.lib().qsp_set_voxel_grid(self.decoder.handle, N.ptr(pts), self.voxels_dim, N.FLAG_HOST_PTRS, None))
+            N.check(self.decoder._L.qsp_set_voxel_grid(self.decoder.handle, N.ptr(pts), self.voxels_dim, N.FLAG_HOST_PTRS, None))
             self.decoder._voxel_grid_tag = tag
 
     def decode_grid(self, codes) -> np.ndarray:

@@ -281,7 +281,34 @@ def _decoder_with_env(decoder_state, **env):
                 os.environ[k] = v
 
 
-def test_cta_pair_kernels_are_bit_identical_to_single_cta(decoder_state):
+@pytest.fixture
+def exp_lib():
+    """The -DQSP_EXPERIMENTAL build of the library (superseded decoder kernels behind QSP_TC_* switches); built by
+    __graft_entry__.build() next to the product library, which carries none of them."""
+    import os
+    from qsp_slam_b200 import _native as N, build
+    if not os.path.isfile(build.LIB_EXP):
+        pytest.skip("libqsp_recon_exp.so is not built")
+    with N.use_library(build.LIB_EXP):
+        yield
+
+
+def test_product_library_carries_one_decoder_family():
+    """The shipped library holds the CTA-pair first-pass kernel, the three-product kernel and the exact-fp32
+    CUDA-core kernel only; the superseded kernels live in the experimental build."""
+    import subprocess
+    from qsp_slam_b200 import build
+    try:
+        out = subprocess.run(["cuobjdump", "-sass", build.LIB], capture_output=True, text=True, timeout=300).stdout
+    except Exception:
+        pytest.skip("cuobjdump not available")
+    fns = [l.split("Function :")[1].strip() for l in out.splitlines() if "Function :" in l]
+    dec = sorted(f for f in fns if "k_decoder" in f)
+    assert len(dec) == 5 and not any("k_decoder_t3" in f for f in dec), dec
+    assert sum("k_decoder_tc" in f for f in dec) == 1 and sum("k_decoder_p3" in f for f in dec) == 2
+
+
+def test_cta_pair_kernels_are_bit_identical_to_single_cta(decoder_state, exp_lib):
     """cta_group::2 changes who streams which half of a weight tile, not the arithmetic: same MMA shapes
     per row, same accumulation order.  Sizes include ragged tails and an odd tile count (surplus tile of a pair)."""
     pair = _decoder_with_env(decoder_state, QSP_TC_PAIR="1", QSP_TC_P3="0", QSP_TC_T3=None)
@@ -296,9 +323,10 @@ def test_cta_pair_kernels_are_bit_identical_to_single_cta(decoder_state):
         s0, j0 = single.decode_sdf_jacobian(z, x, mode="tensor")
         np.testing.assert_array_equal(s1, s0)
         np.testing.assert_array_equal(j1, j0)
+    pair.close(); single.close()
 
 
-def test_three_product_kernel_matches_four_product(decoder_state, orc):
+def test_three_product_kernel_matches_four_product(decoder_state, orc, exp_lib):
     """k_decoder_t3 (W_hi*[X_hi|X_lo] + W_lo*X_hi) against k_decoder_tc<TC_SPLIT> and the fp64 oracle."""
     G, _ = orc
     t3 = _decoder_with_env(decoder_state, QSP_TC_T3="1", QSP_TC_P3="0")
@@ -314,6 +342,7 @@ def test_three_product_kernel_matches_four_product(decoder_state, orc):
         assert np.abs(s3 - s64.numpy()).max() < 3e-5 and np.abs(s3 - s4).max() < 3e-5
         assert rows_close(j3[:, :67], g64.numpy(), 2e-4, max_bad_rows=0.02)
         assert np.abs(t3.decode_sdf(z, x, mode="tensor") - s64.numpy()).max() < 3e-5
+    t3.close(); ref.close()
 
 
 def test_empty_inputs_fail_softly(dev, decoder_state):
@@ -342,7 +371,7 @@ def test_empty_inputs_fail_softly(dev, decoder_state):
 
 
 
-def test_three_product_pair_kernel_vs_fp64_oracle(decoder_state, orc):
+def test_three_product_pair_kernel_vs_fp64_oracle(decoder_state, orc, exp_lib):
     """k_decoder_p3 (the default fp16-pair kernel: M = 128 CTA-pair MMAs, X_hi*W_hi + X_lo*W_hi + X_hi*W_lo with the small
     terms in their own accumulator) against the fp64 oracle, and against the four-product kernel it replaces: it must
     be at least as accurate.  Ragged sizes, an odd number of tiles (surplus tile of a pair), several codes."""
@@ -370,6 +399,7 @@ def test_three_product_pair_kernel_vs_fp64_oracle(decoder_state, orc):
     for c in range(3):
         ref = G.decode_sdf(fd64, torch.from_numpy(codes[c]), torch.from_numpy(x)).numpy()
         assert np.abs(got[c] - ref).max() < 1e-5
+    p3.close(); p4.close()
 
 
 @pytest.mark.parametrize("name,style,samples", [("kitti0", "kitti", 50), ("redwood1", "redwood", 50),
