@@ -331,7 +331,12 @@ extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_
   int r = upload(d, w8, &d->dw.w8);
   if (r) { qsp_decoder_destroy(d); return r; }
   d->dw.b8 = w->lin8_bias[0];
-  if ((r = build_tc_images(d, Wall)) || (r = upload(d, bias_all, &d->tc.bias))) { qsp_decoder_destroy(d); return r; }
+  std::vector<float> bias16_all(bias_all);
+  for (float& v : bias16_all) v *= TC_SA;
+  if ((r = build_tc_images(d, Wall)) || (r = upload(d, bias_all, &d->tc.bias)) || (r = upload(d, bias16_all, &d->tc.bias16))) {
+    qsp_decoder_destroy(d);
+    return r;
+  }
   d->tc.w8 = d->dw.w8;
   d->tc.b8 = d->dw.b8;
   CK(cudaFuncSetAttribute(k_decoder_tc<TC_FAST, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));

@@ -18,6 +18,7 @@
 // Roles, barriers and the weight ring are those of k_decoder_tc<.., CG = 2>.
 #pragma once
 #include <cuda_fp16.h>
+#include <type_traits>
 #include "common.cuh"
 #include "tc_common.cuh"
 #include "decoder_tc.cuh"
@@ -45,8 +46,7 @@ k_decoder_p3(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
   uint64_t* a_ready = bars + 16;                         // [8]
   uint64_t* a_free = bars + 24;                          // [8]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 32);
-  float* sbias = reinterpret_cast<float*>(bars + 64);    // [512] bias of the current layer
-  float* part = sbias;                                   // [4][64] lin8 partial sums (aliases sbias)
+  float* part = reinterpret_cast<float*>(bars + 64);     // [4][64] lin8 partial sums
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const long n = n_dev ? (long)(*n_dev) : n_host;
@@ -166,7 +166,7 @@ k_decoder_p3(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
     const int ptl = (q & 1) * 32 + lane;                 // local point 0..63: A' rows ptl (hi) and 64 + ptl (lo)
     const int kbo = (q >> 1) * 2 + g;                    // this thread's K-block within an accumulator half
     uint32_t it = 0;
-    uint32_t mask[8][4];                                 // ReLU masks: [layer][half*2 + chunk], bit j = column j of the chunk
+    uint32_t mask[8][4];                                 // ReLU masks: [layer][half*2 + chunk], bit 31 - j = column j of the chunk
 
     // 32 consecutive features (chunk `c16`.. of K-block kb) of this thread's point -> hi and lo rows of A'
     auto store_feats = [&](const float* f, int kb, int cc, float sc) {
@@ -175,7 +175,7 @@ k_decoder_p3(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
       for (int u = 0; u < 4; ++u) {
         uint32_t hi[4], lo[4];
 #pragma unroll
-        for (int w = 0; w < 4; ++w) split2(f[8 * u + 2 * w] * sc, f[8 * u + 2 * w + 1] * sc, hi[w], lo[w]);
+        for (int w = 0; w < 4; ++w) split2_fh(f[8 * u + 2 * w] * sc, f[8 * u + 2 * w + 1] * sc, hi[w], lo[w]);
         *reinterpret_cast<uint4*>(blk + sw128_offset(ptl, cc * 4 + u)) = make_uint4(hi[0], hi[1], hi[2], hi[3]);
         *reinterpret_cast<uint4*>(blk + sw128_offset(64 + ptl, cc * 4 + u)) = make_uint4(lo[0], lo[1], lo[2], lo[3]);
       }
@@ -226,25 +226,24 @@ k_decoder_p3(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
       }
       float sdf_v = 0.f;
 
-      for (int s = 0; s < NSTEPS; ++s, ++it) {
-        const uint32_t par = it & 1;
-        const bool fwd = s < 8;
-        const int l = fwd ? s : 15 - s;
-        const int nh = tc_step_halves(s);
-        const bool last = s + 1 == NSTEPS;
-        const bool rewrite = !(fwd && l == 7) && !last;
-        if (fwd) {                                       // bias of this layer -> smem (all epilogue threads)
-          const int e = tid - 64;
-          asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI) : "memory");
-          *reinterpret_cast<float2*>(sbias + 2 * e) = __ldg(reinterpret_cast<const float2*>(dw.bias + l * QSP_HID + 2 * e));
-          asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI) : "memory");
-        }
-        if (s == 15) asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI) : "memory");   // skip-gradient writes of step 11 are read below
-        float psum = 0.f;
+      // One step of the epilogue, specialised by KIND so that every variant is straight-line code from the TMEM load to
+      // the shared-memory store (a common tail after an if/else chain made the compiler funnel the 32 values of a
+      // chunk through register moves at every join):
+      //   0 forward layer (l = 0,1,2,4,5,6)   1 forward l = 3 (skip concat)    2 forward l = 7 (lin8 dot, no rewrite)
+      //   3 reverse step (l = 7,6,5,3,2,1)    4 reverse l = 4 (skip gradient)  5 reverse l = 0 (Jacobian rows out)
+      // The elementwise arithmetic on the accumulators runs as packed fp32 pairs (sm_100 FADD2 / FFMA2 / FMUL2: IEEE
+      // round-to-nearest per lane, i.e. the scalar results, in half the issue slots).
+      float psum = 0.f;
+      auto do_step = [&](auto kind_tag, const int l, const uint32_t par) {
+        constexpr int KIND = decltype(kind_tag)::value;
+        constexpr bool FWD = KIND <= 2;
+        constexpr bool REWRITE = KIND != 2 && KIND != 5;
+        constexpr int NH = KIND == 5 ? 1 : 2;
+#pragma unroll
         for (int h = 0; h < 2; ++h) {
           mbar_wait(&acc_full[h], par);
           tc_fence_after();
-          if (h < nh) {
+          if (h < NH) {
             const int kb = h * 4 + kbo;
             uint32_t va[32], vb[32];                     // large-term and small-term accumulators of a chunk
             const uint32_t tbase = tmem + ((uint32_t)(q * 32) << 16) + h * 128 + g * 64;
@@ -254,34 +253,44 @@ k_decoder_p3(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
             for (int cc = 0; cc < 2; ++cc) {
               const int feat0 = kb * 64 + cc * 32;       // first of this chunk's 32 output features
               tmem_ld_wait();
-              float f[32];
+              uint64_t f2[16];
 #pragma unroll
-              for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(va[j]) + __uint_as_float(vb[j]);
+              for (int j = 0; j < 16; ++j) f2[j] = f32x2_add(f32x2_pack(va[2 * j], va[2 * j + 1]), f32x2_pack(vb[2 * j], vb[2 * j + 1]));
               if (cc == 0) { tmem_ld32(tbase + 32, va); tmem_ld32(tbase + 256 + 32, vb); }   // in flight under the arithmetic
-              if (fwd) {
-                const float inv = 1.f / (TC_SA * TC_SW);
+              float f[32];
+              if constexpr (FWD) {
+                // Activations are kept pre-scaled by TC_SA (the scale their fp16 pair is stored with): acc / TC_SW +
+                // TC_SA * bias = TC_SA * (W x + b) exactly (powers of two), so the rewrite below needs no multiply.
+                // TC_SA * bias comes straight from L1 (a warp reads one address: broadcast), no staging barriers.
+                const uint64_t inv2 = f32x2_pack(__float_as_uint(1.f / TC_SW), __float_as_uint(1.f / TC_SW));
+                const ulonglong2* bp = reinterpret_cast<const ulonglong2*>(dw.bias16 + l * QSP_HID + feat0);
                 uint32_t mb = 0u;
 #pragma unroll
                 for (int j4 = 0; j4 < 8; ++j4) {
-                  const float4 bv = *reinterpret_cast<const float4*>(sbias + feat0 + j4 * 4);
-                  const float bb[4] = {bv.x, bv.y, bv.z, bv.w};
+                  const ulonglong2 bv = __ldg(bp + j4);
+                  float x[4];
+                  f32x2_unpack(f32x2_fma(f2[2 * j4], inv2, bv.x), x[0], x[1]);       // deep_sdf_decoder.py:91
+                  f32x2_unpack(f32x2_fma(f2[2 * j4 + 1], inv2, bv.y), x[2], x[3]);
 #pragma unroll
                   for (int u = 0; u < 4; ++u) {
-                    const int j = j4 * 4 + u;
-                    const float x = fmaf(f[j], inv, bb[u]);                   // deep_sdf_decoder.py:91
-                    if (JAC && x > 0.f) mb |= 1u << j;
-                    f[j] = fmaxf(x, 0.f);                                     // :103
+                    const float y = fmaxf(x[u], 0.f);                                // :103 (max(-0, +0) = +0 in PTX)
+                    f[j4 * 4 + u] = y;
+                    // x > 0  <=>  the bits of y are non-zero  <=>  bit 31 of (bits + 0x7fffffff); shifted into the
+                    // mask from the right: two integer operations per value, column j ends up at bit 31 - j
+                    if (JAC) mb = __funnelshift_l(__float_as_uint(y) + 0x7fffffffu, mb, 1);
                   }
                 }
                 if (JAC) mask[l][h * 2 + cc] = mb;
-                if (l == 3 && feat0 + 32 > QSP_SKIP_COL) {                    // :87-88 concat [h3, code, xyz]
+                if constexpr (KIND == 1) {
+                  if (feat0 + 32 > QSP_SKIP_COL) {                                   // :87-88 concat [h3, code, xyz]
 #pragma unroll
-                  for (int j = 0; j < 32; ++j) {
-                    const int c = feat0 + j - QSP_SKIP_COL;
-                    if (c >= 0) f[j] = !valid ? 0.f : c < QSP_CODE ? my_code[c] : pts[prow * 3 + (c - QSP_CODE)];
+                    for (int j = 0; j < 32; ++j) {
+                      const int c = feat0 + j - QSP_SKIP_COL;
+                      if (c >= 0) f[j] = !valid ? 0.f : TC_SA * (c < QSP_CODE ? my_code[c] : pts[prow * 3 + (c - QSP_CODE)]);
+                    }
                   }
                 }
-                if (l == 7) {                                                 // lin8: 512 -> 1
+                if constexpr (KIND == 2) {                                           // lin8: 512 -> 1
 #pragma unroll
                   for (int j4 = 0; j4 < 8; ++j4) {
                     const float4 wv = __ldg(reinterpret_cast<const float4*>(dw.w8 + feat0 + j4 * 4));
@@ -289,38 +298,49 @@ k_decoder_p3(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
                     psum = fmaf(f[j4 * 4 + 2], wv.z, psum); psum = fmaf(f[j4 * 4 + 3], wv.w, psum);
                   }
                 }
-              } else {
-                // reverse sweep: acc = SG*SW * dX.  Keep SG*dX for the next layer, mask by lin(l-1)'s ReLU.
-                if (l == 0) {                                                 // d sdf / d [code, xyz]
-                  if (valid && feat0 < QSP_JSTRIDE) {
+              } else if constexpr (KIND == 5) {
+                // reverse sweep, last step: d sdf / d [code, xyz] = acc / (SW SG) + the skip gradient of step l = 4
+                if (valid && feat0 < QSP_JSTRIDE) {
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                      const int c = feat0 + j;
-                      if (c < QSP_JSTRIDE) {
-                        float* o = jac_out + (size_t)grow * QSP_JSTRIDE + c;
-                        *o = c < QSP_IN ? f[j] * (1.f / (TC_SW * TC_SG)) + *o : 0.f;
-                      }
+                  for (int j = 0; j < 32; ++j) {
+                    const int c = feat0 + j;
+                    if (c < QSP_JSTRIDE) {
+                      float lo_, hi_;
+                      f32x2_unpack(f2[j >> 1], lo_, hi_);
+                      float* o = jac_out + (size_t)grow * QSP_JSTRIDE + c;
+                      *o = c < QSP_IN ? ((j & 1) ? hi_ : lo_) * (1.f / (TC_SW * TC_SG)) + *o : 0.f;
                     }
                   }
-                } else {
-                  if (l == 4 && feat0 + 32 > QSP_SKIP_COL) {                  // gradient of the re-concatenated input
+                }
+              } else {
+                // reverse sweep: acc = SG*SW * dX.  Keep SG*dX for the next layer, mask by lin(l-1)'s ReLU.
+                if constexpr (KIND == 4) {
+                  if (feat0 + 32 > QSP_SKIP_COL) {                                   // gradient of the re-concatenated input
 #pragma unroll
                     for (int j = 0; j < 32; ++j) {
                       const int c = feat0 + j - QSP_SKIP_COL;
                       if (c >= 0) {
-                        if (valid) jac_out[(size_t)grow * QSP_JSTRIDE + c] = f[j] * (1.f / (TC_SW * TC_SG));
-                        f[j] = 0.f;
+                        float lo_, hi_;
+                        f32x2_unpack(f2[j >> 1], lo_, hi_);
+                        if (valid) jac_out[(size_t)grow * QSP_JSTRIDE + c] = ((j & 1) ? hi_ : lo_) * (1.f / (TC_SW * TC_SG));
+                        f2[j >> 1] = (j & 1) ? f32x2_pack(__float_as_uint(lo_), 0u) : f32x2_pack(0u, __float_as_uint(hi_));
                       }
                     }
                   }
-                  const uint32_t mw = mask[l - 1][h * 2 + cc];
+                }
+                const uint64_t isw2 = f32x2_pack(__float_as_uint(1.f / TC_SW), __float_as_uint(1.f / TC_SW));
+                const uint32_t mw = mask[l - 1][h * 2 + cc];
 #pragma unroll
-                  for (int j = 0; j < 32; ++j) f[j] = ((mw >> j) & 1u) ? f[j] * (1.f / TC_SW) : 0.f;
+                for (int j = 0; j < 16; ++j) {
+                  float lo_, hi_;
+                  f32x2_unpack(f32x2_mul(f2[j], isw2), lo_, hi_);
+                  f[2 * j] = ((mw >> (31 - 2 * j)) & 1u) ? lo_ : 0.f;
+                  f[2 * j + 1] = ((mw >> (30 - 2 * j)) & 1u) ? hi_ : 0.f;
                 }
               }
-              if (rewrite) {
+              if constexpr (REWRITE) {
                 if (cc == 0) mbar_wait(&a_free[kb], par);  // this step's MMAs are done with K-block kb
-                store_feats(f, kb, cc, fwd ? TC_SA : 1.f);
+                store_feats(f, kb, cc, 1.f);
                 if (cc == 1) { fence_proxy_async(); warp_arrive(&a_ready[kb]); }
               }
             }
@@ -328,10 +348,26 @@ k_decoder_p3(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
           tc_fence_before();
           warp_arrive(&acc_free[h]);
         }
+      };
+
+      for (int s = 0; s < NSTEPS; ++s, ++it) {
+        const uint32_t par = it & 1;
+        const bool fwd = s < 8;
+        const int l = fwd ? s : 15 - s;
+        if (s == 15) asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI) : "memory");   // skip-gradient writes of step 11 are read below
+        if (fwd) {
+          if (l == 3) do_step(std::integral_constant<int, 1>{}, l, par);
+          else if (l == 7) { psum = 0.f; do_step(std::integral_constant<int, 2>{}, l, par); }
+          else do_step(std::integral_constant<int, 0>{}, l, par);
+        } else if constexpr (JAC) {
+          if (l == 4) do_step(std::integral_constant<int, 4>{}, l, par);
+          else if (l == 0) do_step(std::integral_constant<int, 5>{}, l, par);
+          else do_step(std::integral_constant<int, 3>{}, l, par);
+        }
         if (fwd && l == 7) {
           // ---- tanh head (deep_sdf_decoder.py:107-108): the four owners of a point's features combine their sums ----
-          asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI) : "memory");             // everybody is done with sbias
-          part[kbo * 64 + ptl] = psum;
+          asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI) : "memory");             // the previous tile's sums have been read
+          part[kbo * 64 + ptl] = psum * (1.f / TC_SA);                          // the features carry the factor TC_SA
           asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI) : "memory");
           sdf_v = tanhf(dw.b8 + ((part[ptl] + part[64 + ptl]) + (part[128 + ptl] + part[192 + ptl])));
           if (kbo == 0 && valid && sdf_o) sdf_o[prow] = sdf_v;
@@ -348,7 +384,7 @@ k_decoder_p3(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
                 const float4 wv = __ldg(reinterpret_cast<const float4*>(dw.w8 + feat0 + j4 * 4));
                 const float ww[4] = {wv.x, wv.y, wv.z, wv.w};
 #pragma unroll
-                for (int u = 0; u < 4; ++u) gsd[j4 * 4 + u] = ((mw >> (j4 * 4 + u)) & 1u) ? d * ww[u] : 0.f;
+                for (int u = 0; u < 4; ++u) gsd[j4 * 4 + u] = ((mw >> (31 - (j4 * 4 + u))) & 1u) ? d * ww[u] : 0.f;
               }
               if (cc == 0) mbar_wait(&a_free[kb], par);
               store_feats(gsd, kb, cc, 1.f);

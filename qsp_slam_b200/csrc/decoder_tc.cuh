@@ -52,6 +52,7 @@ struct TcDecoderDev {
   const uint8_t* img_split;                       // forward then reverse images, (hi, lo) interleaved per tile
   const uint8_t* img_t3;                          // k_decoder_t3: [128 m][64 k] images, (step, half, k-block, M-tile, hi/lo)
   const float* bias;                              // [8][512] fp32, zero padded
+  const float* bias16;                            // [8][512] TC_SA * bias (k_decoder_p3 keeps activations pre-scaled)
   const float* w8;                                // [512] fp32
   float b8;
   const int* row_map;                             // optional (k_decoder_tc forward only): row i reads pts[row_map[i]] and
@@ -68,6 +69,20 @@ __device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t&
   float2 hf = __half22float2(h);
   __half2 l = __floats2half2_rn(a - hf.x, b - hf.y);
   hi = *reinterpret_cast<uint32_t*>(&h);
+  lo = *reinterpret_cast<uint32_t*>(&l);
+}
+
+// The same split with the lo parts by one mixed-precision FMA each (sm_100 FHFMA: f16 * f16 + f32 -> f32):
+// lo = x - hi = hi * (-1) + x, exact in fp32 (the difference of x and its 11-bit rounding has <= 13 significant bits);
+// 4 instructions per pair of values instead of 6 (pack, 2 x unpack, 2 x subtract, pack), bit-identical results.
+__device__ __forceinline__ void split2_fh(float a, float b, uint32_t& hi, uint32_t& lo) {
+  __half2 h = __floats2half2_rn(a, b);
+  hi = *reinterpret_cast<uint32_t*>(&h);
+  const unsigned short h0 = (unsigned short)(hi & 0xffffu), h1 = (unsigned short)(hi >> 16), m1 = 0xbc00;   // -1.0
+  float la, lb;
+  asm("fma.rn.f32.f16 %0, %1, %2, %3;" : "=f"(la) : "h"(h0), "h"(m1), "f"(a));
+  asm("fma.rn.f32.f16 %0, %1, %2, %3;" : "=f"(lb) : "h"(h1), "h"(m1), "f"(b));
+  __half2 l = __floats2half2_rn(la, lb);
   lo = *reinterpret_cast<uint32_t*>(&l);
 }
 
