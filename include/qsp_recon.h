@@ -39,7 +39,8 @@ enum {
   QSP_FLAG_SYNC = 2,         /* cudaStreamSynchronize before returning */
   QSP_FLAG_FAST_FP16 = 4,    /* qsp_decode_sdf only: single-pass fp16 operands (|err| ~ 3e-4), 3-4x faster */
   QSP_FLAG_FP32_CORES = 8,   /* decode calls: exact-fp32 CUDA-core kernel instead of the tensor-core one */
-  QSP_FLAG_EXACT_GRID = 16   /* qsp_extract_mesh only: fp32-equivalent SDF at every grid point (validation) */
+  QSP_FLAG_EXACT_GRID = 16,  /* qsp_extract_mesh only: fp32-equivalent SDF at every grid point (validation) */
+  QSP_FLAG_MESH_TETS = 32    /* mesh calls: marching tetrahedra (round-1 extractor) instead of marching cubes */
 };
 
 /* Arithmetic of the decoder inside the GN loop.  TENSOR (default): tcgen05 tensor-core kernel with
@@ -173,8 +174,10 @@ int qsp_point_pose_jacobian(int32_t device, const float* pts, int32_t n, int32_t
 
 /* --- isosurface extraction: replaces reconstruct/utils.py:120-141 convert_sdf_voxels_to_mesh ------- */
 /* sdf (D,D,D) row-major (the grid decode of qsp_decode_sdf over create_voxel_grid(D));           */
-/* vertices (V,3) float32 = array index * spacing + origin, faces (F,3) int32.  Marching           */
-/* tetrahedra, not scikit-image's Lewiner tables (same zero level set, different triangulation).  */
+/* vertices (V,3) float32 = array index * spacing + origin, faces (F,3) int32.  Marching cubes:    */
+/* one vertex per grid edge with a sign change, as the reference's mesh has (Lewiner's tables add */
+/* rare interior vertices); the case table is our own (gen_mc_table.py) - scikit-image is absent, */
+/* so the TRIANGULATION is unpinned.  QSP_FLAG_MESH_TETS: marching tetrahedra instead.            */
 typedef struct qsp_mesh qsp_mesh;
 int qsp_mesh_extract(const float* sdf, int32_t D, float level, float spacing, const float* origin,
                      uint32_t flags, void* stream, qsp_mesh** out);

@@ -18,6 +18,7 @@ FLAG_FP32_CORES = 8
 PREC_TENSOR = 0
 PREC_FP32_CORES = 1
 FLAG_EXACT_GRID = 16
+FLAG_MESH_TETS = 32
 MODE_FLAGS = {"tensor": 0, "fast": FLAG_FAST_FP16, "fp32": FLAG_FP32_CORES}
 CODE_LEN = 64
 JAC_STRIDE = 68

@@ -8,7 +8,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB = os.path.join(HERE, "libqsp_recon.so")
 LIB_EXP = os.path.join(HERE, "libqsp_recon_exp.so")     # -DQSP_EXPERIMENTAL: adds the superseded decoder kernels (A/B tests)
 SOURCES = [os.path.join(HERE, "csrc", "api.cu")]
-HEADERS = [os.path.join(HERE, "csrc", f) for f in ("common.cuh", "decoder_ffma.cuh", "decoder_tc.cuh", "decoder_t3.cuh", "decoder_p3.cuh", "tc_common.cuh", "gn_kernels.cuh", "mesh_kernels.cuh")] + \
+HEADERS = [os.path.join(HERE, "csrc", f) for f in ("common.cuh", "decoder_ffma.cuh", "decoder_tc.cuh", "decoder_t3.cuh", "decoder_p3.cuh", "tc_common.cuh", "gn_kernels.cuh", "mesh_kernels.cuh", "mc_table.inc")] + \
           [os.path.join(os.path.dirname(HERE), "include", "qsp_recon.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-shared"]

@@ -1331,7 +1331,7 @@ static int scan_ints(const int* in, int* out, long n, int* seg_tmp, cudaStream_t
 }
 
 static int mesh_from_device_grid(const float* src, int32_t D, float level, float spacing, const float* origin,
-                                 cudaStream_t st, qsp_mesh** out) {
+                                 cudaStream_t st, bool tets, qsp_mesh** out) {
   int dev = 0;
   CK(cudaGetDevice(&dev));
   int r = pool_ready(dev);
@@ -1353,9 +1353,11 @@ static int mesh_from_device_grid(const float* src, int32_t D, float level, float
   CKM(cudaMallocAsync(&tbase, (Cn + 1) * 4, st));
   CKM(cudaMallocAsync(&seg, (2 * nseg + 2) * 4, st));
   const int tb = 256;
-  k_mt_vertex_flags<<<(unsigned)((V + tb - 1) / tb), tb, 0, st>>>(src, D, level, vmask, vcount); LAUNCHED();
+  k_mt_vertex_flags<<<(unsigned)((V + tb - 1) / tb), tb, 0, st>>>(src, D, level, tets ? MESH_EDGES_TETS : MESH_EDGES_CUBES, vmask, vcount); LAUNCHED();
   scan_ints(vcount, vbase, (long)V, seg, st);
-  k_mt_cells<false><<<(unsigned)((Cn + tb - 1) / tb), tb, 0, st>>>(src, D, level, vmask, vbase, tcount, nullptr, nullptr); LAUNCHED();
+  if (tets) k_mt_cells<false><<<(unsigned)((Cn + tb - 1) / tb), tb, 0, st>>>(src, D, level, vmask, vbase, tcount, nullptr, nullptr);
+  else k_mc_cells<false><<<(unsigned)((Cn + tb - 1) / tb), tb, 0, st>>>(src, D, level, vmask, vbase, tcount, nullptr, nullptr);
+  LAUNCHED();
   scan_ints(tcount, tbase, (long)Cn, seg, st);
   CKM(cudaMemcpyAsync(&m->nv, vbase + V, 4, cudaMemcpyDeviceToHost, st));
   CKM(cudaMemcpyAsync(&m->nf, tbase + Cn, 4, cudaMemcpyDeviceToHost, st));
@@ -1364,7 +1366,9 @@ static int mesh_from_device_grid(const float* src, int32_t D, float level, float
   CKM(cudaMallocAsync(&m->faces, (size_t)std::max(m->nf, 1) * 12, st));
   k_mt_vertices<<<(unsigned)((V + tb - 1) / tb), tb, 0, st>>>(src, D, level, spacing, origin[0], origin[1], origin[2],
                                                               vmask, vbase, m->verts); LAUNCHED();
-  k_mt_cells<true><<<(unsigned)((Cn + tb - 1) / tb), tb, 0, st>>>(src, D, level, vmask, vbase, nullptr, tbase, m->faces); LAUNCHED();
+  if (tets) k_mt_cells<true><<<(unsigned)((Cn + tb - 1) / tb), tb, 0, st>>>(src, D, level, vmask, vbase, nullptr, tbase, m->faces);
+  else k_mc_cells<true><<<(unsigned)((Cn + tb - 1) / tb), tb, 0, st>>>(src, D, level, vmask, vbase, nullptr, tbase, m->faces);
+  LAUNCHED();
   CKM(cudaGetLastError());
   cleanup();
   CKM(cudaStreamSynchronize(st));
@@ -1378,7 +1382,8 @@ extern "C" int qsp_mesh_extract(const float* sdf, int32_t D, float level, float 
                                 uint32_t flags, void* stream, qsp_mesh** out) {
   if (!sdf || !origin || !out || D < 2 || D > 1024) { g_err = "bad argument"; return QSP_ERR_INVALID; }
   cudaStream_t st = (cudaStream_t)stream;
-  if (!(flags & QSP_FLAG_HOST_PTRS)) return mesh_from_device_grid(sdf, D, level, spacing, origin, st, out);
+  const bool tets = flags & QSP_FLAG_MESH_TETS;
+  if (!(flags & QSP_FLAG_HOST_PTRS)) return mesh_from_device_grid(sdf, D, level, spacing, origin, st, tets, out);
   int dev = 0;
   CK(cudaGetDevice(&dev));
   int r = pool_ready(dev);
@@ -1388,7 +1393,7 @@ extern "C" int qsp_mesh_extract(const float* sdf, int32_t D, float level, float 
   CK(cudaMallocAsync(&dsdf, V * 4, st));
   cudaError_t e = cudaMemcpyAsync(dsdf, sdf, V * 4, cudaMemcpyHostToDevice, st);
   if (e != cudaSuccess) { g_err = std::string("cudaMemcpyAsync: ") + cudaGetErrorString(e); cudaFreeAsync(dsdf, st); return QSP_ERR_CUDA; }
-  r = mesh_from_device_grid(dsdf, D, level, spacing, origin, st, out);
+  r = mesh_from_device_grid(dsdf, D, level, spacing, origin, st, tets, out);
   cudaFreeAsync(dsdf, st);
   return r;
 }
@@ -1449,7 +1454,7 @@ extern "C" int qsp_extract_mesh(qsp_decoder* d, const float* code, float level, 
   }
   if (sdf_out)
     CK(cudaMemcpyAsync(sdf_out, sdf, V * 4, (flags & QSP_FLAG_HOST_PTRS) ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice, st));
-  return mesh_from_device_grid(sdf, D, level, spacing, origin, st, out);
+  return mesh_from_device_grid(sdf, D, level, spacing, origin, st, (flags & QSP_FLAG_MESH_TETS) != 0, out);
 }
 
 extern "C" int qsp_mesh_sizes(const qsp_mesh* m, int32_t* n_vertices, int32_t* n_faces) {

@@ -1,18 +1,25 @@
 // Isosurface extraction from the decoded SDF grid (the step after
 // reconstruct/optimizer.py:296).  The reference calls scikit-image's Lewiner marching cubes on the CPU
-// (reconstruct/utils.py:120-141); its case tables are not reproducible here, so this is marching
-// TETRAHEDRA on the Kuhn subdivision of every cell (6 tetrahedra around the 000-111 diagonal): the
-// same zero level set, vertices on grid edges (axis edges, face diagonals and the body diagonal) by
-// linear interpolation, unique vertices, faces oriented with the normal towards increasing SDF.
+// (reconstruct/utils.py:120-141).  Default here: MARCHING CUBES with one vertex on every grid edge that has a
+// sign change (linear interpolation) - the vertex set of the reference's mesh, up to the rare interior vertices
+// Lewiner's tables add - and a case table derived by gen_mc_table.py (scikit-image is absent, its tables are not
+// restated: the triangulation is unpinned).  QSP_FLAG_MESH_TETS selects the round-1 extractor instead: marching
+// TETRAHEDRA on the Kuhn subdivision of every cell (6 tetrahedra around the 000-111 diagonal), which also puts
+// vertices on face and body diagonals (2-3x the triangles).  Both: unique vertices, watertight, faces oriented with
+// the normal towards increasing SDF.
 // Output contract as the reference: vertices (V,3) float32 = index * spacing + origin, faces (F,3) int32.
 #pragma once
 #include "common.cuh"
+#include "mc_table.inc"
+
+#define MESH_EDGES_CUBES 0x0Bu     // edge types 0, 1, 3: the three axis edges of a grid vertex
+#define MESH_EDGES_TETS 0x7Fu      // + face diagonals and the body diagonal
 
 // edge type t (0..6) joins a grid vertex with the vertex at offset bits (t+1) = (dx | dy<<1 | dz<<2),
 // where x is the slowest array axis (index = (x*D + y)*D + z)
 __device__ __forceinline__ int mt_lin(int x, int y, int z, int D) { return (x * D + y) * D + z; }
 
-__global__ void k_mt_vertex_flags(const float* __restrict__ sdf, int D, float level,
+__global__ void k_mt_vertex_flags(const float* __restrict__ sdf, int D, float level, unsigned edge_types,
                                   unsigned char* __restrict__ vmask, int* __restrict__ vcount) {
   int v = blockIdx.x * blockDim.x + threadIdx.x;
   if (v >= D * D * D) return;
@@ -21,7 +28,7 @@ __global__ void k_mt_vertex_flags(const float* __restrict__ sdf, int D, float le
   unsigned m = 0;
   for (int t = 0; t < 7; ++t) {
     int b = t + 1, nx = x + (b & 1), ny = y + ((b >> 1) & 1), nz = z + ((b >> 2) & 1);
-    if (nx < D && ny < D && nz < D) {
+    if (((edge_types >> t) & 1u) && nx < D && ny < D && nz < D) {
       bool in1 = sdf[mt_lin(nx, ny, nz, D)] < level;
       if (in0 != in1) m |= 1u << t;
     }
@@ -136,6 +143,33 @@ __global__ void k_mt_cells(const float* __restrict__ sdf, int D, float level,
     }
   }
   if (!WRITE) tcount[c] = n;
+}
+
+// Marching cubes: the cell's 8 corner states select a row of the generated table; a triangle corner is the crossing on
+// one of the 12 cube edges, i.e. the vertex of an axis edge of one of the cell's corners.
+template <bool WRITE>
+__global__ void k_mc_cells(const float* __restrict__ sdf, int D, float level,
+                           const unsigned char* __restrict__ vmask, const int* __restrict__ vbase,
+                           int* __restrict__ tcount, const int* __restrict__ tbase, int* __restrict__ faces) {
+  int c = blockIdx.x * blockDim.x + threadIdx.x;
+  const int C = D - 1;
+  if (c >= C * C * C) return;
+  int z = c % C, y = (c / C) % C, x = c / (C * C);
+  unsigned inside = 0;
+#pragma unroll
+  for (int b = 0; b < 8; ++b)
+    if (sdf[mt_lin(x + (b & 1), y + ((b >> 1) & 1), z + ((b >> 2) & 1), D)] < level) inside |= 1u << b;
+  const int n = c_mc_ntri[inside];
+  if (!WRITE) { tcount[c] = n; return; }
+  int out = tbase[c];
+  for (int t = 0; t < n; ++t)
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+      const int e = c_mc_tri[inside][3 * t + k], a = c_mc_edges[e][0], b = c_mc_edges[e][1];
+      const int v = mt_lin(x + (a & 1), y + ((a >> 1) & 1), z + ((a >> 2) & 1), D);
+      const int ty = (b ^ a) - 1;                          // axis edge type of corner a: 0, 1 or 3
+      faces[(out + t) * 3 + k] = vbase[v] + __popc(vmask[v] & ((1u << ty) - 1u));
+    }
 }
 
 // ------------------------------------------------------------------------------------------------

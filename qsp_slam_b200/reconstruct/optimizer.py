@@ -263,9 +263,11 @@ class MeshExtractor(object):
         sdf = sdf.reshape(-1, D, D, D)
         return sdf[0] if single else sdf
 
-    def extract_mesh_from_code(self, code, exact_grid: bool = False):
+    def extract_mesh_from_code(self, code, exact_grid: bool = False, method: str = "cubes"):
         """optimizer.py:292-304: grid decode, then marching cubes at level 0 with spacing 2/(D-1) and
-        origin (-1,-1,-1) (utils.py:120-141).  vertices (V,3) float32, faces (F,3) int32.
+        origin (-1,-1,-1) (utils.py:120-141).  vertices (V,3) float32, faces (F,3) int32.  The vertices are those of
+        the reference's Lewiner mesh (one per sign-changing grid edge); the triangulation comes from our own case
+        table and is unpinned (scikit-image absent).  ``method="tets"``: marching tetrahedra.
         One native call (qsp_extract_mesh): the grid never leaves the device, and only the grid points whose value
         the isosurface depends on get the fp32-equivalent evaluation - the mesh is bit-identical to the one of the
         exact grid (``exact_grid=True``, the validation path)."""
@@ -273,16 +275,16 @@ class MeshExtractor(object):
         self._ensure_device_grid()
         voxel_size = 2.0 / (self.voxels_dim - 1)
         code = N.f32(code).reshape(-1)[:self.code_len]
-        vertices, faces = extract_mesh(self.decoder.handle, code, 0.0, voxel_size, (-1.0, -1.0, -1.0), exact_grid)
+        vertices, faces = extract_mesh(self.decoder.handle, code, 0.0, voxel_size, (-1.0, -1.0, -1.0), exact_grid, method=method)
         return ForceKeyErrorDict(vertices=vertices, faces=faces)
 
-    def extract_mesh_from_code_reference_grid(self, code):
+    def extract_mesh_from_code_reference_grid(self, code, method: str = "cubes"):
         """The unfused form of the reference: ``decode_grid`` (fp32-equivalent everywhere, grid returned to the
         host) followed by the isosurface kernels on that host grid.  Kept for the tests."""
         from ..mesh import marching_cubes
         sdf = self.decode_grid(code)
         voxel_size = 2.0 / (self.voxels_dim - 1)
-        vertices, faces = marching_cubes(sdf, 0.0, voxel_size, (-1.0, -1.0, -1.0))
+        vertices, faces = marching_cubes(sdf, 0.0, voxel_size, (-1.0, -1.0, -1.0), method=method)
         return ForceKeyErrorDict(vertices=vertices.astype("float32"), faces=faces.astype("int32"))
 
     def extract_meshes_from_codes(self, codes):

@@ -1,6 +1,8 @@
-"""Mesh extraction (marching tetrahedra) on the GPU against the CPU loop implementation and against
-level-set properties.  Parity with the reference's scikit-image Lewiner mesh is unpinned (skimage is
-absent in both environments); see oracle/mesh_oracle.py."""
+"""Mesh extraction on the GPU - marching cubes (default) and marching tetrahedra - against the CPU loop
+implementations and against level-set properties.  The marching-cubes VERTEX SET is pinned: one vertex per grid edge
+with a sign change, computed independently in numpy (what scikit-image's Lewiner routine of the reference
+interpolates, utils.py:131).  The triangulation is unpinned (skimage is absent in both environments); see
+oracle/mesh_oracle.py."""
 import numpy as np
 import pytest
 import torch
@@ -26,9 +28,70 @@ def same_mesh(v, f, vr, fr, tol=1e-4):
     return a == b
 
 
-def test_sphere_and_random_field_match_cpu_marching_tets():
+def test_sphere_and_random_field_match_cpu_marching_cubes():
     from qsp_slam_b200.mesh import marching_cubes
+    from oracle.mesh_oracle import marching_cubes_ref, sign_change_vertices
+    D = 11
+    lin = np.linspace(-1, 1, D, dtype=np.float32)
+    X, Y, Z = np.meshgrid(lin, lin, lin, indexing="ij")
+    fields = [np.sqrt(X ** 2 + Y ** 2 + Z ** 2) - 0.63,
+              np.random.default_rng(0).standard_normal((D, D, D)).astype(np.float32)]
+    for sdf in fields:
+        sdf = sdf.astype(np.float32)
+        v, f = marching_cubes(sdf, 0.0, 2.0 / (D - 1))
+        vr, fr = marching_cubes_ref(sdf, 0.0, 2.0 / (D - 1))
+        assert v.dtype == np.float32 and f.dtype == np.int32 and v.shape[1] == 3 and f.shape[1] == 3
+        assert v.shape[0] == vr.shape[0] and f.shape[0] == len(fr)
+        assert f.min() >= 0 and f.max() < v.shape[0]
+        # same vertices in the same order, same triangles in the same order (cell-major, table order)
+        assert np.abs(v.astype(np.float64) - vr).max() < 1e-6
+        assert np.array_equal(f, np.asarray(fr, np.int32))
+        # the vertex set is exactly the set of sign-changing grid edges (independent numpy computation)
+        sv = sign_change_vertices(sdf, 0.0, 2.0 / (D - 1))
+        assert sv.shape == v.shape and np.abs(v.astype(np.float64) - sv).max() < 1e-6
+        assert np.unique(f).size == v.shape[0]            # every vertex is used
+
+
+def test_marching_cubes_vertex_set_on_a_decoded_grid(decoder_state):
+    """On the SDF grid of the decoder itself (D = 48): vertices == the sign-changing grid edges (positions within 1e-6,
+    same order), the surface is a closed 2-manifold wherever it does not leave the cube, and marching tetrahedra on
+    the same grid produce 2-3x the triangles (the reason for the switch)."""
+    from qsp_slam_b200.decoder import DeviceDecoder
+    from qsp_slam_b200.reconstruct.optimizer import MeshExtractor
+    from qsp_slam_b200.mesh import marching_cubes
+    from oracle.mesh_oracle import sign_change_vertices
+    D = 48
+    mx = MeshExtractor(DeviceDecoder(decoder_state, 0), 64, D)
+    code = (np.random.default_rng(1).standard_normal(64) * 0.05).astype(np.float32)
+    sdf = mx.decode_grid(code)
+    v, f = marching_cubes(sdf, 0.0, 2.0 / (D - 1))
+    sv = sign_change_vertices(sdf, 0.0, 2.0 / (D - 1))
+    assert v.shape == sv.shape and v.shape[0] > 1000
+    assert np.abs(v.astype(np.float64) - sv).max() < 1e-6
+    e = np.sort(np.concatenate([f[:, [0, 1]], f[:, [1, 2]], f[:, [2, 0]]]), axis=1)
+    _, cnt = np.unique(e, axis=0, return_counts=True)
+    assert cnt.max() <= 2                                    # 2-manifold: no edge with more than two triangles
+    # edges with a single triangle can only lie on the boundary of the cube (open surface there)
+    ue = np.unique(e, axis=0)
+    single = ue[cnt == 1]
+    if single.size:
+        on_boundary = (np.abs(np.abs(v[single.reshape(-1)]) - 1.0) < 1e-6).any(1)
+        assert on_boundary.all()
+    # consistent orientation: every interior directed edge has its opposite
+    de = np.concatenate([f[:, [0, 1]], f[:, [1, 2]], f[:, [2, 0]]])
+    fwd = set(map(tuple, de.tolist()))
+    assert len(fwd) == de.shape[0]
+    assert sum((b, a) in fwd for a, b in fwd) == len(fwd) - single.shape[0]
+    m = mx.extract_mesh_from_code(code)
+    assert np.array_equal(m.vertices, v) and np.array_equal(m.faces, f)
+    vt, ft = marching_cubes(sdf, 0.0, 2.0 / (D - 1), method="tets")
+    assert 1.8 * f.shape[0] < ft.shape[0] < 3.5 * f.shape[0] and vt.shape[0] > 2 * v.shape[0]
+
+
+def test_sphere_and_random_field_match_cpu_marching_tets():
+    from qsp_slam_b200.mesh import marching_cubes as _mc
     from oracle.mesh_oracle import marching_tets
+    marching_cubes = lambda *a: _mc(*a, method="tets")  # noqa: E731
     D = 11
     lin = np.linspace(-1, 1, D, dtype=np.float32)
     X, Y, Z = np.meshgrid(lin, lin, lin, indexing="ij")
@@ -44,8 +107,10 @@ def test_sphere_and_random_field_match_cpu_marching_tets():
         assert same_mesh(v, f, vr, fr)
 
 
-def test_sphere_mesh_properties():
-    from qsp_slam_b200.mesh import marching_cubes
+@pytest.mark.parametrize("method", ["cubes", "tets"])
+def test_sphere_mesh_properties(method):
+    from qsp_slam_b200.mesh import marching_cubes as _mc
+    marching_cubes = lambda *a: _mc(*a, method=method)  # noqa: E731
     D = 48
     lin = np.linspace(-1, 1, D, dtype=np.float32)
     X, Y, Z = np.meshgrid(lin, lin, lin, indexing="ij")
