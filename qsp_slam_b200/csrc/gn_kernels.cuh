@@ -400,7 +400,7 @@ __global__ void k_render(ObjState* __restrict__ st, const float* __restrict__ ra
       const float exact = fz.g_sdf[fz.row0 + k], err = fabsf(q_sdf[qi] - exact);
       q_sdf[qi] = exact;
       emax = fmaxf(emax, err);
-      nexc += err > lim34;
+      nexc += lim34 > 0.f && err > lim34;             // (no margin: the first pass is the exact kernel itself)
     }
     if (ce > cb) {
 #pragma unroll
