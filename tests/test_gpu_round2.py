@@ -118,7 +118,7 @@ def test_candidate_overflow_fails_objects_not_the_call(golden, decoder_state):
     names = ["kitti0", "kitti1", "redwood0", "redwood1"]
     dets = _dets(golden, names)
     ref = _decoder_with_env(decoder_state, QSP_BAND_CAP=None)
-    opt_ref = make_opt(ref, "kitti", 2)
+    opt_ref = make_opt(ref, "kitti", 1)                           # one iteration: the candidate counts of iteration 0 decide
     opt_ref.set_debug(True)
     rec_ref = opt_ref.reconstruct_objects_records(dets)
     n_cand = [opt_ref.get_iteration(0, b)["n_cand"] for b in range(4)]
@@ -126,7 +126,7 @@ def test_candidate_overflow_fails_objects_not_the_call(golden, decoder_state):
     assert all(rec_ref[:, 80] == 1.0) and ref.call_stats()["overflow"] == 0
     cap = n_cand[0] + n_cand[1] + n_cand[2] // 2                  # object 2 does not fit, object 3 is beyond
     small = _decoder_with_env(decoder_state, QSP_BAND_CAP=str(cap))
-    opt = make_opt(small, "kitti", 2)
+    opt = make_opt(small, "kitti", 1)
     with warnings.catch_warnings(record=True) as w:
         warnings.simplefilter("always")
         rec = opt.reconstruct_objects_records(dets)               # must not raise
