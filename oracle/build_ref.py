@@ -1,8 +1,9 @@
 """TEST INFRASTRUCTURE ONLY - builds the UNMODIFIED reference hot path into ``oracle/_ref/``.
 
 The reference's hot path is Python, so "building it from the sources where they lie" means byte-compiling the
-files under ``/root/reference`` (``py_compile``, same interpreter as the GPU box: same image) into sourceless
-modules ``oracle/_ref/<package>/<module>.pyc``.  No reference source is copied into the repository; ``oracle/_ref/``
+files under ``/root/reference`` (``compile`` + ``marshal``, same interpreter as the GPU box: same image) into
+``oracle/_ref/<package>/<module>.refbin`` (a neutral extension: the snapshot sent to the GPU box drops ``*.pyc``);
+``oracle/ref_harness.py`` installs an importer for them.  No reference source is copied into the repository; ``oracle/_ref/``
 is git-ignored but NOT gpurun-ignored, so the compiled modules travel to the GPU box like our own ``.so``.
 ``__graft_entry__.build()`` runs this when ``/root/reference`` is present (i.e. in the build container).
 
@@ -13,8 +14,8 @@ that compare against the reference itself instead of the port.
 from __future__ import annotations
 
 import json
+import marshal
 import os
-import py_compile
 import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
@@ -34,9 +35,12 @@ def build(verbose: bool = True) -> str | None:
     manifest = {"python": sys.version.split()[0], "files": {}}
     for rel in FILES:
         src = os.path.join(REFERENCE_ROOT, rel)
-        dst = os.path.join(OUT, rel + "c")                       # X.py -> X.pyc next to where X.py would be
+        dst = os.path.join(OUT, rel[:-3] + ".refbin")            # X.py -> X.refbin: the marshalled module code object
         os.makedirs(os.path.dirname(dst), exist_ok=True)
-        py_compile.compile(src, cfile=dst, dfile=rel, doraise=True, invalidation_mode=py_compile.PycInvalidationMode.UNCHECKED_HASH)
+        with open(src, "rb") as f:
+            code = compile(f.read(), rel, "exec", dont_inherit=True)
+        with open(dst, "wb") as f:
+            marshal.dump(code, f)
         manifest["files"][rel] = os.path.getsize(src)
     with open(os.path.join(OUT, "MANIFEST.json"), "w") as f:
         json.dump(manifest, f, indent=1)

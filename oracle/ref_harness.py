@@ -29,9 +29,45 @@ def reference_root():
     """Directory to import the reference from: its sources if present, else the byte-compiled copy."""
     if os.path.isfile(os.path.join(REFERENCE_ROOT, "reconstruct", "optimizer.py")):
         return REFERENCE_ROOT
-    if os.path.isfile(os.path.join(COMPILED_ROOT, "reconstruct", "optimizer.pyc")):
+    if os.path.isfile(os.path.join(COMPILED_ROOT, "reconstruct", "optimizer.refbin")):
         return COMPILED_ROOT
     return None
+
+
+class _RefbinFinder:
+    """Meta-path importer for the byte-compiled reference modules of ``oracle/_ref`` (``<pkg>/<mod>.refbin`` = the
+    marshalled code object of the unmodified source file; ``<pkg>/__init__.refbin`` makes ``<pkg>`` a package)."""
+
+    def __init__(self, root):
+        self.root = root
+
+    def _path(self, fullname):
+        base = os.path.join(self.root, *fullname.split("."))
+        if os.path.isfile(os.path.join(base, "__init__.refbin")):
+            return os.path.join(base, "__init__.refbin"), True
+        if os.path.isfile(base + ".refbin"):
+            return base + ".refbin", False
+        return None, False
+
+    def find_spec(self, fullname, path=None, target=None):
+        import importlib.util
+        p, is_pkg = self._path(fullname)
+        if p is None:
+            return None
+        spec = importlib.util.spec_from_loader(fullname, self, origin=p, is_package=is_pkg)
+        if is_pkg:
+            spec.submodule_search_locations = [os.path.dirname(p)]
+        return spec
+
+    def create_module(self, spec):
+        return None
+
+    def exec_module(self, module):
+        import marshal
+        with open(module.__spec__.origin, "rb") as f:
+            code = marshal.load(f)
+        module.__file__ = module.__spec__.origin
+        exec(code, module.__dict__)
 
 
 def available() -> bool:
@@ -95,9 +131,12 @@ def load():
     torch.cuda.synchronize = lambda *a, **k: None
     torch.cuda.empty_cache = lambda *a, **k: None
 
-    for p in (root, os.path.join(root, "reconstruct")):
-        if p not in sys.path:
-            sys.path.insert(0, p)
+    if root == COMPILED_ROOT:
+        sys.meta_path.insert(0, _RefbinFinder(root))
+    else:
+        for p in (root, os.path.join(root, "reconstruct")):
+            if p not in sys.path:
+                sys.path.insert(0, p)
     warnings.filterwarnings("ignore")
     import reconstruct.optimizer as r_opt
     import reconstruct.loss as r_loss

@@ -857,9 +857,12 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
   // Small batches: the surface rows (M of them, known up front) get their own fwd+Jacobian launch on the side stream,
   // on ceil(M / 64) SMs, while the first pass of the ray samples runs on the others; the candidate rows follow on the
   // main stream.  Rows are independent of their tile, so the results are those of the single launch, bit for bit.
+  // Worth it only while the first pass is short: its grid gives up the side launch's SMs for its whole duration (a
+  // Redwood call with 4 096 x 128 samples, or four hypotheses of it, loses more there than the side launch saves).
   const int surf_tiles = (M + 63) / 64;
+  const long first_tiles_max = ((long)R * S + 127) / 128;
   const bool conc = d->concurrent && d->fused && hp_mode == DEC_SPLIT && !d->debug && !d->timeline && M > 0 &&
-                    2 * surf_tiles <= d->num_sms;
+                    4 * surf_tiles <= d->num_sms && first_tiles_max <= 8L * d->num_sms;
   const int surf_grid = (surf_tiles + 1) / 2 * 2;
   const int first_grid_cap = conc ? std::max(2, d->pair_grid - surf_grid) : 0;
   std::vector<std::pair<const char*, cudaEvent_t>> marks;   // diagnostic timeline of the last iteration

@@ -4,7 +4,7 @@ set -u
 MODE=${1:-full}
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.limit --format=csv > gpurun_out/smi.txt 2>&1
-nproc > gpurun_out/nproc.txt
+nproc > gpurun_out/nproc.txt; ls -R oracle/_ref > gpurun_out/ref_files.txt 2>&1
 timeout 1800 python -m pytest tests -m gpu -q --timeout 900 -p no:cacheprovider > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
 tail -40 gpurun_out/pytest_gpu.log
 timeout 900 python bench.py --steps 10 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"; tail -5 gpurun_out/bench.err
@@ -23,7 +23,7 @@ if [ "$MODE" = "full" ]; then
   timeout 900 python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-configs > gpurun_out/plain_bench.log 2>&1 &&
   timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 1200 --csv --log-file gpurun_out/launches.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-configs > gpurun_out/ncu_bench.log 2>&1; echo "ncu launches rc=$?"
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_decoder_ -c 4 -o gpurun_out/decoder_tc -f \
+  QSP_CALIBRATE=0 timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_decoder_ -c 4 -o gpurun_out/decoder_tc -f \
     python scripts/profile_decoder.py $ROWS > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?"
 fi
 ls -la gpurun_out

@@ -29,6 +29,11 @@ def _worker(rank, world, port, n_obj, q):
     local = torch.tensor([[float(i)] * sharding.RECORD_LEN for i in mine], dtype=torch.float32).reshape(-1, sharding.RECORD_LEN)
     allr = sharding.gather_records(local, [len(r) for r in ranks])
     ordered = sharding.scatter_back(allr.numpy(), ranks)
+    # the preallocated form gives the same rows, also when called repeatedly (buffers reused)
+    g = sharding.RecordGatherer([len(r) for r in ranks], "cpu")
+    for _ in range(2):
+        g.gather(local)
+        assert torch.equal(g.ordered(), allr)
     if rank == 0:
         q.put(ordered[:, 0].tolist())
     dist.barrier()
@@ -51,6 +56,25 @@ def test_balanced_order_is_a_permutation_and_balanced():
     assert sorted(i for x in r for i in x) == list(range(57))
     loads = [sum(costs[i] for i in x) for x in r]
     assert max(loads) - min(loads) <= max(costs)
+
+
+def test_balanced_equal_counts_and_cost_proxy():
+    costs = list(np.random.default_rng(1).integers(1, 100, 64).astype(float))
+    r = sharding.balanced_equal_counts(costs, 8)
+    assert sorted(i for x in r for i in x) == list(range(64)) and all(len(x) == 8 for x in r)
+    loads = [sum(costs[i] for i in x) for x in r]
+    assert max(loads) - min(loads) <= max(costs)
+    r3 = sharding.balanced_equal_counts(costs[:10], 3)
+    assert sorted(len(x) for x in r3) == [3, 3, 4]
+    # the cost proxy counts the depth samples inside the unit ball at the initial pose
+    from qsp_slam_b200 import synth
+    T = np.eye(4, dtype=np.float32)
+    T[:3, :3] *= 2.0
+    T[2, 3] = 10.0
+    rays = np.array([[0.0, 0.0, 1.0], [1.0, 0.0, 1.0]], np.float32)      # through the centre / missing the ball
+    c = sharding.inball_cost(dict(t_cam_obj=T, rays=rays), 101)
+    assert abs(c - 100.0) < 1e-6                                          # the whole depth range of the central ray
+    assert sharding.inball_cost(dict(t_cam_obj=T, rays=np.zeros((0, 3), np.float32)), 50) == 0.0
 
 
 def test_gather_two_ranks_gloo():
