@@ -161,7 +161,7 @@ def build_decoder(state_np):
     wrapped = torch.nn.DataParallel(dec)
     sd = {"module." + k: torch.from_numpy(v.copy()) for k, v in state_np.items()}
     wrapped.load_state_dict(sd)
-    dec = wrapped.module
+    dec = wrapped.module.cpu()          # DataParallel moves the module to cuda:0 on a GPU box; this arm is the CPU path
     dec.eval()
     return dec
 

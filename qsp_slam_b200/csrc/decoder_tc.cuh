@@ -354,6 +354,15 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
         const int nh = tc_step_halves(s);
         const bool last = s + 1 == NSTEPS;
         const bool rewrite = !(fwd && l == 7) && !last;
+        if (fwd) {                                       // bias of this layer -> smem (all epilogue threads)
+          // (reading the bias straight from L1 instead, as k_decoder_p3 does, measured 4.5 % SLOWER here: 0.570 ->
+          // 0.596 ms on 231 k rows - this epilogue is short and the loads' latency is exposed)
+          TP_MARK(0);
+          asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI) : "memory");
+          if (e < 256) *reinterpret_cast<float2*>(sbias + 2 * e) = __ldg(reinterpret_cast<const float2*>(dw.bias + l * QSP_HID + 2 * e));
+          asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI) : "memory");
+          TP_MARK(8);
+        }
         if (s == 15) asm volatile("bar.sync 1, %0;" ::"n"(TC_EPI) : "memory");   // skip-gradient writes of step 11 are read below
         float psum = 0.f;
         uint32_t mbits[4] = {0u, 0u, 0u, 0u};
@@ -411,8 +420,7 @@ k_decoder_tc(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
                 const float inv = MODE == TC_SPLIT ? 1.f / (TC_SA * TC_SW) : 1.f;
 #pragma unroll
                 for (int j4 = 0; j4 < CW / 4; ++j4) {
-                  // bias straight from L1 (a warp reads one address: broadcast): no staging, no barriers per layer
-                  const float4 bv = __ldg(reinterpret_cast<const float4*>(dw.bias + l * QSP_HID + colb + j4 * 4));
+                  const float4 bv = *reinterpret_cast<const float4*>(sbias + colb + j4 * 4);
                   const float bb[4] = {bv.x, bv.y, bv.z, bv.w};
 #pragma unroll
                   for (int u = 0; u < 4; ++u) {
