@@ -114,6 +114,7 @@ class CpuArm:
         self.kind = "port"
         self.fd = G.FoldedDecoder(state)
         self.prm = G.Params(cfg)
+        self.rh = rh
         if rh.available() and not force_port:
             try:
                 ref = rh.load()
@@ -121,17 +122,21 @@ class CpuArm:
                 self.kind = "reference"
             except Exception as e:  # a broken oracle/_ref must not take the bench line down
                 print(f"bench: reference import failed ({e!r}); timing the oracle port", file=sys.stderr)
+            finally:
+                rh.restore_cuda()       # the harness patches Tensor.cuda process-wide: only while the reference runs
 
     def run(self, objs, kind=None):
         """-> (results [dict(is_good, t_cam_obj, code, loss)], seconds)"""
         kind = kind or self.kind
         out = []
         t0 = time.perf_counter()
-        for o in objs:
-            if kind == "reference":
-                r = self.opt.reconstruct_object(o["t_cam_obj"].copy(), o["pts"], o["rays"], o["depth"])
-                out.append(dict(is_good=bool(r.is_good), t_cam_obj=r.t_cam_obj, code=r.code, loss=float(r.loss)))
-            else:
+        if kind == "reference":
+            with self.rh.cpu_only():    # .cuda() -> identity only inside this block (the GPU arm shares the process)
+                for o in objs:
+                    r = self.opt.reconstruct_object(o["t_cam_obj"].copy(), o["pts"], o["rays"], o["depth"])
+                    out.append(dict(is_good=bool(r.is_good), t_cam_obj=r.t_cam_obj, code=r.code, loss=float(r.loss)))
+        else:
+            for o in objs:
                 out.append(self.G.reconstruct_object(self.fd, self.prm, o["t_cam_obj"], o["pts"], o["rays"], o["depth"]))
         return out, time.perf_counter() - t0
 

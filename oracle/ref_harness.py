@@ -104,6 +104,42 @@ class _AttrDict(dict):
 
 
 _loaded = None
+_saved_cuda = None
+
+
+def patch_cuda():
+    """The reference hard-codes ``.cuda()`` (optimizer.py:120-136,151; loss.py:32,63,84,101-109): for the CPU arm
+    ``Tensor.cuda`` / ``Module.cuda`` become the identity and ``torch.cuda.synchronize / empty_cache`` no-ops.  These
+    are PROCESS-WIDE patches: a process that also drives the GPU (bench.py, the GPU tests) must call
+    ``restore_cuda()`` after running the reference - or use ``cpu_only()`` - before it touches CUDA tensors again."""
+    global _saved_cuda
+    import torch
+    if _saved_cuda is None:
+        _saved_cuda = (torch.Tensor.cuda, torch.nn.Module.cuda, torch.cuda.synchronize, torch.cuda.empty_cache)
+    torch.Tensor.cuda = lambda self, *a, **k: self
+    torch.nn.Module.cuda = lambda self, *a, **k: self
+    torch.cuda.synchronize = lambda *a, **k: None
+    torch.cuda.empty_cache = lambda *a, **k: None
+
+
+def restore_cuda():
+    global _saved_cuda
+    import torch
+    if _saved_cuda is not None:
+        torch.Tensor.cuda, torch.nn.Module.cuda, torch.cuda.synchronize, torch.cuda.empty_cache = _saved_cuda
+        _saved_cuda = None
+
+
+class cpu_only:
+    """``with cpu_only(): ...`` - the patches of ``patch_cuda`` for the duration of the block."""
+
+    def __enter__(self):
+        patch_cuda()
+        return self
+
+    def __exit__(self, *exc):
+        restore_cuda()
+        return False
 
 
 def load():
@@ -126,10 +162,7 @@ def load():
     sys.modules.setdefault("skimage", sk)
     sys.modules.setdefault("skimage.measure", skm)
 
-    torch.Tensor.cuda = lambda self, *a, **k: self
-    torch.nn.Module.cuda = lambda self, *a, **k: self
-    torch.cuda.synchronize = lambda *a, **k: None
-    torch.cuda.empty_cache = lambda *a, **k: None
+    patch_cuda()
 
     if root == COMPILED_ROOT:
         sys.meta_path.insert(0, _RefbinFinder(root))

@@ -72,6 +72,14 @@ def test_oracle_render_term_ignores_samples_behind_an_opaque_one(golden, decoder
 @pytest.mark.parametrize("name", NAMES)
 def test_reference_render_loss_ignores_samples_behind_an_opaque_one(golden, decoder_state, name, monkeypatch):
     ref = ref_harness.load()
+    ref_harness.patch_cuda()                                    # the reference hard-codes .cuda(); undone below
+    try:
+        _body(ref, golden, decoder_state, name, monkeypatch)
+    finally:
+        ref_harness.restore_cuda()
+
+
+def _body(ref, golden, decoder_state, name, monkeypatch):
     torch.set_num_threads(1)
     decoder = ref_harness.build_decoder(decoder_state)
     t_oc, rays, sampled, dobs, z = _inputs(golden, name)
