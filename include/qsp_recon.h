@@ -167,6 +167,17 @@ int qsp_rotation_prior(int32_t device, const float* t_obj_cam, float* out8);
 int qsp_exp_map(int32_t device, const float* x, int32_t n, int32_t se3, float* out);
 /* loss_utils.py:250-265 get_robust_res + :236-247 huber_norm_weights: res (n) -> robust (n), w (n), loss (1)   */
 int qsp_robust_res(int32_t device, const float* res, int32_t n, float b, float* robust, float* w, float* loss);
+/* No counterpart in the reference: added for callers that cannot allocate
+ * (CUDA graph capture, tight serving loops).  get_robust_res as above, but res / robust / w / loss are DEVICE
+ * pointers on `device`, the work is queued on `stream` (0 = default stream, not synchronised), and the call performs
+ * no cudaMalloc / cudaFree: the per-block partial sums of the loss live in a fixed file-scope device array
+ * (16.25 KB, held by every GPU that loads the library until exit).  1 <= n <= QSP_NOALLOC_MAX_N, larger n is
+ * rejected with QSP_ERR_INVALID.  robust and w are bit-identical to qsp_robust_res; the loss is summed block by
+ * block (fixed order, repeatable) and agrees to fp32 rounding of the sum.  Every call shares the one array: calls
+ * that overlap on the GPU (different streams, different threads) race - serialise them.                        */
+#define QSP_NOALLOC_MAX_N 4194304
+int qsp_robust_res_noalloc(int32_t device, const float* res, int32_t n, float b, float* robust, float* w,
+                           float* loss, void* stream);
 /* loss_utils.py:40-48 sdf_to_occupancy                                                                         */
 int qsp_sdf_to_occupancy(int32_t device, const float* sdf, int64_t n, float th, float* out);
 /* loss_utils.py:166-185 get_points_to_pose_jacobian_sim3 (se3 = 0, out (n,3,7)) / :107-126 _se3 (out (n,3,6))  */

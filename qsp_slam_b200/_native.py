@@ -23,10 +23,11 @@ MODE_FLAGS = {"tensor": 0, "fast": FLAG_FAST_FP16, "fp32": FLAG_FP32_CORES}
 CODE_LEN = 64
 JAC_STRIDE = 68
 RECORD_LEN = 82
+NOALLOC_MAX_N = 4194304                    # QSP_NOALLOC_MAX_N of include/qsp_recon.h
 
 EXPORTS = ["qsp_decoder_create", "qsp_decoder_destroy", "qsp_decode_sdf", "qsp_decode_sdf_jacobian",
            "qsp_reconstruct_batch", "qsp_get_call_stats", "qsp_estimate_pose_batch", "qsp_set_precision", "qsp_set_first_pass_margin", "qsp_check_guards", "qsp_guard_selftest", "qsp_set_debug", "qsp_get_iteration",
-           "qsp_get_band_indices", "qsp_get_loss_rows", "qsp_rotation_prior", "qsp_exp_map", "qsp_robust_res", "qsp_sdf_to_occupancy", "qsp_point_pose_jacobian", "qsp_mesh_extract", "qsp_set_voxel_grid", "qsp_extract_mesh", "qsp_mesh_sizes", "qsp_mesh_copy", "qsp_mesh_free", "qsp_last_error", "qsp_launch_count", "qsp_kernel_ms", "qsp_version"]
+           "qsp_get_band_indices", "qsp_get_loss_rows", "qsp_rotation_prior", "qsp_exp_map", "qsp_robust_res", "qsp_robust_res_noalloc", "qsp_sdf_to_occupancy", "qsp_point_pose_jacobian", "qsp_mesh_extract", "qsp_set_voxel_grid", "qsp_extract_mesh", "qsp_mesh_sizes", "qsp_mesh_copy", "qsp_mesh_free", "qsp_last_error", "qsp_launch_count", "qsp_kernel_ms", "qsp_version"]
 
 _f32p = C.POINTER(C.c_float)
 _i32p = C.POINTER(C.c_int32)
@@ -97,6 +98,7 @@ def _load(path: str):
     L.qsp_rotation_prior.argtypes = [C.c_int32, vp, vp]
     L.qsp_exp_map.argtypes = [C.c_int32, vp, C.c_int32, C.c_int32, vp]
     L.qsp_robust_res.argtypes = [C.c_int32, vp, C.c_int32, C.c_float, vp, vp, vp]
+    L.qsp_robust_res_noalloc.argtypes = [C.c_int32, vp, C.c_int32, C.c_float, vp, vp, vp, vp]
     L.qsp_sdf_to_occupancy.argtypes = [C.c_int32, vp, C.c_int64, C.c_float, vp]
     L.qsp_point_pose_jacobian.argtypes = [C.c_int32, vp, C.c_int32, C.c_int32, vp]
     L.qsp_mesh_extract.argtypes = [vp, C.c_int32, C.c_float, C.c_float, vp, C.c_uint32, vp, C.POINTER(vp)]

@@ -1480,3 +1480,107 @@ extern "C" void qsp_mesh_free(qsp_mesh* m) {
   cudaFreeAsync(m->faces, m->stream);
   delete m;
 }
+
+// ------------------------------------------------------------------------------------------------
+// get_robust_res without any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops).  Device pointers in
+// and out; the per-block partial sums of the loss and the block ticket live in a file-scope device array that every
+// GPU loading the library holds until exit.  All calls share it: calls that overlap on the GPU race.
+// ------------------------------------------------------------------------------------------------
+#define NOALLOC_ROWS_PER_BLOCK 1024
+#define NOALLOC_MAX_BLOCKS 4096                                    // -> QSP_NOALLOC_MAX_N = 4 194 304 residuals
+#define NOALLOC_SCRATCH_FLOATS (NOALLOC_MAX_BLOCKS + 64)           // partial sums, then the ticket (16.25 KB)
+static __device__ __align__(256) float g_noalloc_scratch[NOALLOC_SCRATCH_FLOATS];
+
+// Multi-block form of k_util_robust: robust / w as there; the loss from per-block partial sums that the last block to
+// finish (ticket) adds in block order - a fixed summation order, so two calls on the same input agree bit for bit.
+__global__ void __launch_bounds__(256) k_util_robust_noalloc(const float* __restrict__ res, int n, float b,
+                                                             float* __restrict__ robust, float* __restrict__ w,
+                                                             float* __restrict__ loss, float* __restrict__ scratch) {
+  __shared__ float red[256];
+  __shared__ bool last;
+  float* partial = scratch;
+  unsigned* ticket = reinterpret_cast<unsigned*>(scratch + NOALLOC_MAX_BLOCKS);
+  const int base = blockIdx.x * NOALLOC_ROWS_PER_BLOCK;
+  float acc = 0.f;
+  for (int k = 0; k < NOALLOC_ROWS_PER_BLOCK / 256; ++k) {
+    const int i = base + k * 256 + threadIdx.x;
+    if (i < n) {
+      const float r = res[i], wi = huber_weight(r, b), rr = wi * r;
+      robust[i] = rr;
+      w[i] = wi;
+      acc += rr * rr;
+    }
+  }
+  red[threadIdx.x] = acc;
+  __syncthreads();
+  for (int d = 128; d > 0; d >>= 1) {
+    if (threadIdx.x < d) red[threadIdx.x] += red[threadIdx.x + d];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    partial[blockIdx.x] = red[0];
+    __threadfence();
+    last = atomicAdd(ticket, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (!last) return;
+  __threadfence();
+  acc = 0.f;
+  for (unsigned i = threadIdx.x; i < gridDim.x; i += 256) acc += __ldcg(partial + i);
+  red[threadIdx.x] = acc;
+  __syncthreads();
+  for (int d = 128; d > 0; d >>= 1) {
+    if (threadIdx.x < d) red[threadIdx.x] += red[threadIdx.x + d];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    *loss = red[0] / (float)n;
+    *ticket = 0u;                                                  // left clean for the next call
+  }
+}
+
+namespace {
+constexpr int kNoallocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+float* g_noalloc_ptr[kNoallocMaxDevices] = {};                     // device address of g_noalloc_scratch, per device
+
+// The array's name is a host-side stand-in in host code: the kernel needs the device address, which differs per
+// device.  Looked up once per device with that device current.
+int noalloc_scratch_of(int device, float** out) {
+  if (device < 0 || device >= kNoallocMaxDevices) { g_err = "device index out of range"; return QSP_ERR_INVALID; }
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[device]) {
+    void* p = nullptr;
+    CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+    if (!p) { g_err = "cudaGetSymbolAddress returned a null address"; return QSP_ERR_CUDA; }
+    g_noalloc_ptr[device] = static_cast<float*>(p);
+  }
+  *out = g_noalloc_ptr[device];
+  return QSP_OK;
+}
+}  // namespace
+
+extern "C" int qsp_robust_res_noalloc(int32_t device, const float* res, int32_t n, float b, float* robust, float* w,
+                                      float* loss, void* stream) {
+  if (n <= 0 || !res || !robust || !w || !loss) { g_err = "bad argument (n must be >= 1, all pointers device pointers)"; return QSP_ERR_INVALID; }
+  if (n > QSP_NOALLOC_MAX_N) {
+    g_err = "qsp_robust_res_noalloc: n = " + std::to_string(n) + " exceeds QSP_NOALLOC_MAX_N = " +
+            std::to_string(QSP_NOALLOC_MAX_N) + " (the fixed scratch array); use qsp_robust_res";
+    return QSP_ERR_INVALID;
+  }
+  CK(cudaSetDevice(device));
+  float* scratch = nullptr;
+  int r;
+  if ((r = noalloc_scratch_of(device, &scratch))) return r;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int blocks = (n + NOALLOC_ROWS_PER_BLOCK - 1) / NOALLOC_ROWS_PER_BLOCK;
+  // the ticket must start at zero whatever an earlier (possibly aborted) call left behind; the partial sums are
+  // written before they are read
+  CK(cudaMemsetAsync(scratch + NOALLOC_MAX_BLOCKS, 0, 64 * sizeof(float), st));
+  k_util_robust_noalloc<<<blocks, 256, 0, st>>>(res, n, b, robust, w, loss, scratch);
+  LAUNCHED();
+  CK(cudaGetLastError());
+  return QSP_OK;
+}
+static_assert(QSP_NOALLOC_MAX_N == NOALLOC_MAX_BLOCKS * NOALLOC_ROWS_PER_BLOCK, "header and scratch array disagree");
