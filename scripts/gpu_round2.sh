@@ -5,8 +5,9 @@ MODE=${1:-full}
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.limit --format=csv > gpurun_out/smi.txt 2>&1
 nproc > gpurun_out/nproc.txt; ls -R oracle/_ref > gpurun_out/ref_files.txt 2>&1
+timeout 300 python -m pytest tests/test_zz_no_alloc.py -m gpu -q -p no:cacheprovider > gpurun_out/pytest_noalloc_alone.log 2>&1; echo "no-alloc test alone rc=$?"; tail -3 gpurun_out/pytest_noalloc_alone.log
 timeout 1800 python -m pytest tests -m gpu -q --timeout 900 -p no:cacheprovider > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
-tail -40 gpurun_out/pytest_gpu.log
+tail -40 gpurun_out/pytest_gpu.log | tee gpurun_out/pytest_gpu_tail.txt
 timeout 900 python bench.py --steps 10 --warmup 3 > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"; tail -5 gpurun_out/bench.err
 tail -c 6000 gpurun_out/bench.json
 ROWS=$(python -c "import json; r=json.load(open('gpurun_out/bench.json'))['rows_per_iteration']; print(r['first_pass'], r['fwd_jac'])" 2>/dev/null || echo "231460 84672")

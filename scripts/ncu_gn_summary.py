@@ -1,5 +1,5 @@
 """Summarises an `ncu --set full` capture of the Gauss-Newton kernels (b)-(d) of one warm kitti_batch32 iteration
-(gpurun_out/gn_kernels.ncu-rep, written by scripts/gpu_round.sh) into profiles/<tag>_ncu_gn_kernels_summary.txt:
+(gpurun_out/gn_kernels.ncu-rep, written by an `ncu --set full -k regex:k_` pass over scripts/timeline.py) into profiles/<tag>_ncu_gn_kernels_summary.txt:
 per kernel the duration, DRAM bytes read + written, achieved DRAM GB/s (bytes / duration), the share of the measured
 HBM copy bandwidth (MEASURED_PEAKS.json, fallback 6500 GB/s), L2 and SM throughput and the launch shape.
 usage: python scripts/ncu_gn_summary.py r01i"""

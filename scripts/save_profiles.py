@@ -1,17 +1,26 @@
-"""Copies the outputs of scripts/gpu_round.sh from gpurun_out/ (scratch) into profiles/ under a round tag:
+"""Copies the outputs of scripts/gpu_round2.sh from gpurun_out/ (scratch) into profiles/ under a round tag:
 bench line, ncu launch list + per-kernel shares, `ncu --set full` summary of the decoder kernels, config timings,
 in-situ timelines; refreshes profiles/ncu_traffic.json (DRAM bytes per launch, read by bench.py).
-usage: python scripts/save_profiles.py r01h"""
+usage: python scripts/save_profiles.py r02a"""
 import collections, csv, json, os, shutil, subprocess, sys
 tag = sys.argv[1]
 root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 go, pr = os.path.join(root, "gpurun_out"), os.path.join(root, "profiles")
 for src, dst in (("launches.csv", "launches_bench.csv"), ("bench.json", "bench.json"), ("configs.jsonl", "configs.jsonl"),
-                 ("timeline.txt", "timeline_kitti_batch32.txt"), ("timeline_single.txt", "timeline_kitti_single.txt")):
+                 ("timeline.txt", "timeline_kitti_batch32.txt"), ("timeline_single.txt", "timeline_kitti_single.txt"),
+                 ("bench_reference.json", "bench_reference.json"), ("single_ab.jsonl", "single_ab.jsonl"),
+                 ("parity_decompose.md", "parity_decompose.md"), ("profile_decoder.log", "profile_decoder.txt"),
+                 ("fullsize_parity.jsonl", "fullsize_parity.jsonl"), ("fullsize_parity_cases.jsonl", "fullsize_parity_cases.jsonl"),
+                 ("bench_gpus2.json", "bench_gpus2.json"), ("bench_gpus4.json", "bench_gpus4.json"),
+                 ("bench_gpus8.json", "bench_gpus8.json"), ("bench_gpus1_samebox.json", "bench_gpus1_samebox.json"),
+                 ("pytest_gpu_tail.txt", "pytest_gpu_tail.txt"), ("smi.txt", "smi.txt")):
     if os.path.exists(os.path.join(go, src)):
         shutil.copy(os.path.join(go, src), os.path.join(pr, f"{tag}_{dst}"))
 bench = json.load(open(os.path.join(go, "bench.json")))
 rows_it = bench.get("rows_per_iteration", {})
+if not os.path.exists(os.path.join(go, "decoder_tc.ncu-rep")) or not os.path.exists(os.path.join(go, "launches.csv")):
+    print("no ncu outputs in gpurun_out/: copied the plain files only")
+    sys.exit(0)
 raw = subprocess.run(["ncu", "-i", os.path.join(go, "decoder_tc.ncu-rep"), "--page", "raw", "--csv"],
                      capture_output=True, text=True).stdout
 rows = list(csv.reader(raw.splitlines()))
@@ -56,7 +65,7 @@ for r in L[h + 1:]:
     a = agg.setdefault(name, [0, 0.0]); a[0] += 1; a[1] += v
 tot = sum(a[1] for a in agg.values())
 with open(os.path.join(pr, f"{tag}_step_breakdown.txt"), "w") as f:
-    f.write("# per-kernel share of one bench command (python bench.py --steps 2 --warmup 1 --no-cpu-baseline) from the ncu launch list\n"
+    f.write("# per-kernel share of one bench command (python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-configs) from the ncu launch list\n"
             f"# profiles/{tag}_launches_bench.csv (gpu__time_duration.sum; cold-cache, serialised launches: shares, not absolutes)\n")
     f.write(f"{'kernel':44s} {'launches':>8s} {'total ms':>10s} {'avg us':>9s} {'share':>7s}\n")
     for k, a in sorted(agg.items(), key=lambda x: -x[1][1]):
