@@ -95,7 +95,7 @@ struct qsp_decoder {
   Buf in_T, in_code, in_pts, in_rays, in_depth, in_scale, out_rec;
   Buf pts_off, rays_off, depth_off, ray_obj, pt_obj;
   Buf state, counters, ray_cnt, ray_base, band_cnt, band_base;
-  Buf q_pts, q_code, q_samp, cand_q, q_sdf, slot, ray_res, ray_nev, ph_list, ph_code;
+  Buf q_pts, q_code, q_samp, cand_q, q_sdf, slot, ray_res, ray_nev, ray_prev, ray_hint, ph_list, ph_code;
   Buf grid_pts, grid_sdf, grid_need, grid_list, grid_cnt, grid_code;   // qsp_extract_mesh
   int grid_D = 0;
   Buf jp_pts, jp_code, g_sdf, g_jac, row_fac, row_res, row_ray, row_samp, row_active, m_active;
@@ -114,6 +114,8 @@ struct qsp_decoder {
   int t3_grid = 148;
   float margin0 = QSP_FAST_MARGIN0, margin1 = QSP_FAST_MARGIN_PER_NORM;   // first-pass margin = margin0 + margin1 * |code|
   bool phases = true;                              // first pass front to back in phases of 32 samples per ray
+  bool hint = true;                                // phase 0 sized per ray from the previous iteration's first opaque sample
+  int hint_slack = 1;                              // samples decoded beyond that position
   int pre_reduce = -1;                             // QSP_REDUCE=0/1: k_reduce_partials before k_solve (default: when >= 8 chunks)
   bool timeline = false;                           // QSP_TIMELINE=1: CUDA-event time of every launch group of one GN iteration
   bool fused = true;                               // QSP_FUSED=0: the unfused small-kernel sequence (A/B, bit-identical results)
@@ -393,6 +395,8 @@ extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_
   CK(cudaFuncSetAttribute(k_decoder_ffma<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, FF_SMEM_BYTES));
   CK(cudaFuncSetAttribute(k_decoder_ffma<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, FF_SMEM_BYTES));
   if (const char* e = getenv("QSP_PHASES")) d->phases = atoi(e) != 0;
+  if (const char* e = getenv("QSP_HINT")) d->hint = atoi(e) != 0;
+  if (const char* e = getenv("QSP_HINT_SLACK")) d->hint_slack = std::max(0, atoi(e));
   if (const char* e = getenv("QSP_TIMELINE")) d->timeline = atoi(e) != 0;
   if (const char* e = getenv("QSP_REDUCE")) d->pre_reduce = atoi(e) != 0;
   if (const char* e = getenv("QSP_FUSED")) d->fused = atoi(e) != 0;
@@ -417,7 +421,7 @@ static std::vector<std::pair<const char*, Buf*>> all_bufs(qsp_decoder* d) {
   return {NB(in_T), NB(in_code), NB(in_pts), NB(in_rays), NB(in_depth), NB(in_scale), NB(out_rec), NB(pts_off),
           NB(rays_off), NB(depth_off), NB(ray_obj), NB(pt_obj), NB(state), NB(counters), NB(ray_cnt), NB(ray_base),
           NB(band_cnt), NB(band_base), NB(q_pts), NB(q_code), NB(q_samp), NB(cand_q), NB(q_sdf), NB(slot), NB(ray_res),
-          NB(ray_nev), NB(ph_list), NB(ph_code), NB(grid_pts), NB(grid_sdf), NB(grid_need), NB(grid_list), NB(grid_cnt),
+          NB(ray_nev), NB(ray_prev), NB(ray_hint), NB(ph_list), NB(ph_code), NB(grid_pts), NB(grid_sdf), NB(grid_need), NB(grid_list), NB(grid_cnt),
           NB(grid_code), NB(jp_pts), NB(jp_code), NB(g_sdf), NB(g_jac), NB(row_fac), NB(row_res), NB(row_ray),
           NB(row_samp), NB(row_active), NB(m_active), NB(partials), NB(reduced), NB(dbgH), NB(dbgb), NB(dbgdx), NB(blk_tot), NB(blk_base), NB(dec_pts),
           NB(dec_codes), NB(dec_out), NB(dec_jac)};
@@ -784,11 +788,13 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
 
   ObjState* state; int *counters, *ray_obj, *pt_obj, *ray_cnt, *ray_base, *band_cnt, *band_base, *blk_tot, *blk_base;
   float *q_pts, *q_sdf, *slot, *ray_res, *jp_pts, *g_sdf, *g_jac, *row_fac, *row_res, *partials, *d_rec;
-  int *q_code, *q_samp, *cand_q, *jp_code, *row_ray, *row_samp, *ray_nev, *ph_list, *ph_code;
+  int *q_code, *q_samp, *cand_q, *jp_code, *row_ray, *row_samp, *ray_nev, *ray_prev, *ray_hint, *ph_list, *ph_code;
   const int nblk = std::max(1, (R + GN_RAYS_PER_BLOCK - 1) / GN_RAYS_PER_BLOCK);
   ENSURE(d->state, B, state);
   ENSURE(d->counters, 8 + GN_MAXC, counters);
   ENSURE(d->ray_nev, R, ray_nev);
+  ENSURE(d->ray_prev, R, ray_prev);
+  ENSURE(d->ray_hint, R, ray_hint);
   ENSURE(d->ph_list, qcap, ph_list);
   ENSURE(d->ph_code, qcap, ph_code);
   ENSURE(d->ray_obj, R, ray_obj);
@@ -854,6 +860,7 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
   d->stats_fresh = false;
   int* phase_cnt = counters + 8;
   const int n_phases = d->phases ? gn_num_phases(S) : 1;
+  const bool use_hint = d->phases && d->hint && n_phases > 1;   // iteration 0 has no hint: runs of 32
   // Small batches: the surface rows (M of them, known up front) get their own fwd+Jacobian launch on the side stream,
   // on ceil(M / 64) SMs, while the first pass of the ray samples runs on the others; the candidate rows follow on the
   // main stream.  Rows are independent of their tile, so the results are those of the single launch, bit for bit.
@@ -900,7 +907,8 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
     // in phases of 32 samples along the ray; a ray stops at its first certainly-opaque sample (k_phase_list)
     if (d->phases) {
       for (int ph = 0; ph < n_phases; ++ph) {
-        KL(k_phase_list, ray_blocks, tb, st, ph, (int)(ph == n_phases - 1), R, state, ray_obj, ray_base, ray_cnt, q_sdf, q_code, ray_nev, ph_list, ph_code, phase_cnt);
+        KL(k_phase_list, ray_blocks, tb, st, ph, (int)(ph == n_phases - 1), R, state, ray_obj, ray_base, ray_cnt, q_sdf, q_code, ray_nev, ray_prev,
+           (const int*)(use_hint && it > 0 ? ray_hint : nullptr), d->hint_slack, ph_list, ph_code, phase_cnt);
         MARK("k_phase_list");
         if ((r = launch_decoder(d, first_mode, false, q_pts, ph_code, codes_dev, code_stride, 0, phase_cnt + ph, 1, q_sdf, nullptr, st, ph_list, first_grid_cap))) return r;
         MARK("first-pass decoder");
@@ -912,15 +920,15 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
     // candidates near the band, appended behind the surface points in the Jacobian row list
     if (d->fused) {
       KL(k_cand_count, nblk, 32 * GN_RAYS_PER_BLOCK, st, state, ray_obj, ray_base, nev, R, q_sdf, band_cnt, blk_tot, blk_base,
-                                               band_base + R, counters, M, (int)bandcap);
+                                               band_base + R, counters, M, (int)bandcap, use_hint ? ray_hint : nullptr);
       KL(k_cand_fill, nblk, 32 * GN_RAYS_PER_BLOCK, st, state, ray_obj, ray_base, nev, R, q_sdf, band_cnt, blk_base, band_base, M,
                                               (int)bandcap, q_pts, q_code, q_samp, jp_pts, jp_code, row_ray, row_samp, cand_q, counters + 3);
     } else {
       KL(k_candidates<false>, ray_blocks, tb, st, state, ray_obj, ray_base, nev, R, q_sdf, band_cnt, nullptr, M, (int)bandcap, nullptr,
-                                                     nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr);
+                                                     nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, use_hint ? ray_hint : nullptr);
       KL(k_exclusive_scan, 1, 1024, st, band_cnt, band_base, R, counters + 1, M, counters + 2, (int)bandcap);
       KL(k_candidates<true>, ray_blocks, tb, st, state, ray_obj, ray_base, nev, R, q_sdf, nullptr, band_base, M, (int)bandcap, q_pts,
-                                                    q_code, q_samp, jp_pts, jp_code, row_ray, row_samp, cand_q, counters + 3);
+                                                    q_code, q_samp, jp_pts, jp_code, row_ray, row_samp, cand_q, counters + 3, nullptr);
     }
     // (a) SDF + input Jacobian of surface points and candidates (loss.py:34,144), fp32-equivalent
     if (conc) {

@@ -250,15 +250,18 @@ __global__ void k_sample_fused(const ObjState* __restrict__ st, const float* __r
   if (lane == 0) { ray_cnt[r] = cnt; ray_base[r] = base; }
 }
 
-// First pass in phases along the ray (front to back).  Phase p decodes in-ball samples [32p, 32p + 32) (the last
-// phase: up to 32 + GN_PHASE_TAIL) of every
+// First pass in phases along the ray (front to back).  A phase decodes the next run of in-ball samples of every
 // ray that has not met a certainly-opaque sample (first-pass s <= -lim, hence exact s <= -th and occupancy exactly
 // 1, loss_utils.py:46-47) in an earlier phase: behind such a sample the transmittance cumprod(1 - o) is exactly 0
 // (loss.py:99), so those samples weigh 0 in the rendered depth (:106-114) and have de_do = 0 (:118-125) - their SDF
 // is never needed.  One warp per ray appends its rows to the phase's list (order within the list is irrelevant:
 // the decoder scatters through the list) and records how many of the ray's samples have been decoded.
-// The last phase also takes a short tail of up to GN_PHASE_TAIL samples (S = 100: phases of 32, 32, 36 instead of a
-// fourth launch pair for 4 samples per ray).
+// ANY split of a ray into runs gives the same result; the split only decides how many samples BEHIND the opaque one
+// are decoded for nothing.  Runs: 32 samples per phase, the last phase takes what is left (S = 100: 32, 32, 36 -
+// gn_num_phases() folds a tail of <= GN_PHASE_TAIL samples into the last phase instead of a launch pair of its
+// own).  With a hint (ray_hint[r] = position of the ray's first opaque sample in the PREVIOUS GN iteration, written
+// by the candidate kernels; the whole ray when it had none) phase 0 decodes hint + slack samples instead: the pose
+// moves little between iterations, so most rays end inside phase 0 with `slack` wasted samples rather than ~16.
 #define GN_PHASE_TAIL 8
 __host__ __device__ inline int gn_num_phases(int S) {
   const int full = (S + 31) / 32, rem = S - (full - 1) * 32;
@@ -266,21 +269,27 @@ __host__ __device__ inline int gn_num_phases(int S) {
 }
 __global__ void k_phase_list(int p, int last, int R, const ObjState* __restrict__ st, const int* __restrict__ ray_obj,
                              const int* __restrict__ ray_base, const int* __restrict__ ray_cnt, const float* __restrict__ q_sdf,
-                             const int* __restrict__ q_code, int* __restrict__ ray_nev,
+                             const int* __restrict__ q_code, int* __restrict__ ray_nev, int* __restrict__ ray_prev,
+                             const int* __restrict__ ray_hint, int slack,
                              int* __restrict__ list, int* __restrict__ list_code, int* __restrict__ phase_cnt) {
   pdl_prologue();
   int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (r >= R) return;
-  const int lo = ray_base[r], n = ray_cnt[r], start = p * 32;
-  if (p == 0 && lane == 0) ray_nev[r] = 0;
-  if (start >= n) return;
-  if (p > 0) {
+  const int lo = ray_base[r], n = ray_cnt[r];
+  int start = 0;
+  if (p == 0) {
+    if (lane == 0) ray_nev[r] = 0;
+  } else {
+    start = ray_nev[r];
+    if (start >= n) return;
     const float lim = st[ray_obj[r]].cand_lim;
-    const int nev = ray_nev[r];
-    const float s = q_sdf[lo + start - 32 + lane];       // the previous phase's 32 samples of this ray
-    if (__any_sync(0xffffffffu, s <= -lim) || nev != start) return;
+    bool opq = false;
+    for (int i = ray_prev[r] + lane; i < start; i += 32) opq |= q_sdf[lo + i] <= -lim;   // the ray's previous run
+    if (__any_sync(0xffffffffu, opq)) return;
   }
-  const int m = min(last ? 32 + GN_PHASE_TAIL : 32, n - start);
+  if (start >= n) return;
+  const int len = last ? n - start : (p == 0 && ray_hint) ? ray_hint[r] + slack : 32;
+  const int m = min(len, n - start);
   int base = 0;
   if (lane == 0) base = atomicAdd(phase_cnt + p, m);
   base = __shfl_sync(0xffffffffu, base, 0);
@@ -288,7 +297,7 @@ __global__ void k_phase_list(int p, int last, int R, const ObjState* __restrict_
     list[base + k] = lo + start + k;
     list_code[base + k] = q_code[lo + start + k];
   }
-  if (lane == 0) ray_nev[r] = start + m;
+  if (lane == 0) { ray_prev[r] = start; ray_nev[r] = start + m; }
 }
 
 // exclusive scan of n ints into out[0..n] (out[n] = total); single block.  A thread owns SCAN_ITEMS consecutive
@@ -1097,13 +1106,14 @@ __global__ void k_candidates(ObjState* __restrict__ st, const int* __restrict__ 
                              int row0, int cap, const float* __restrict__ q_pts, const int* __restrict__ q_code,
                              const int* __restrict__ q_samp, float* __restrict__ jp_pts, int* __restrict__ jp_code,
                              int* __restrict__ row_ray, int* __restrict__ row_samp, int* __restrict__ cand_q,
-                             int* __restrict__ overflow) {
+                             int* __restrict__ overflow, int* __restrict__ ray_hint = nullptr) {
   pdl_prologue();
   int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (r >= R) return;
   const int lo = ray_base[r], hi = lo + ray_nev[r];     // the decoded samples of the ray (k_phase_list)
   const float lim = st[ray_obj[r]].cand_lim;
   int cnt = 0;
+  int first_opq = hi - lo;                              // k_phase_list's hint for the next iteration
   const int base = FILL ? cand_base[r] : 0;
   for (int i0 = lo; i0 < hi; i0 += 32) {
     int i = i0 + lane;
@@ -1132,9 +1142,12 @@ __global__ void k_candidates(ObjState* __restrict__ st, const int* __restrict__ 
       }
     }
     cnt += __popc(m);
-    if (mo) break;
+    if (mo) { first_opq = i0 - lo + __ffs(mo); break; }
   }
-  if (!FILL && lane == 0) cand_cnt[r] = cnt;
+  if (!FILL && lane == 0) {
+    cand_cnt[r] = cnt;
+    if (ray_hint) ray_hint[r] = first_opq;
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1148,8 +1161,10 @@ __global__ void k_candidates(ObjState* __restrict__ st, const int* __restrict__ 
 #define GN_RAYS_PER_BLOCK 8
 // candidates of one ray (the logic of k_candidates): calls f(i, k) for the k-th candidate, in-ball sample index i
 template <class F>
-__device__ __forceinline__ int for_each_candidate(int lo, int hi, float lim, const float* __restrict__ q_sdf, int lane, F f) {
+__device__ __forceinline__ int for_each_candidate(int lo, int hi, float lim, const float* __restrict__ q_sdf, int lane, F f,
+                                                  int* first_opq = nullptr) {
   int cnt = 0;
+  if (first_opq) *first_opq = hi - lo;                   // samples up to and including the first opaque one (all: none)
   for (int i0 = lo; i0 < hi; i0 += 32) {
     const int i = i0 + lane;
     bool c = false, opq = false;
@@ -1159,7 +1174,10 @@ __device__ __forceinline__ int for_each_candidate(int lo, int hi, float lim, con
     const unsigned m = __ballot_sync(0xffffffffu, c);
     if (c) f(i, cnt + __popc(m & ((1u << lane) - 1u)));
     cnt += __popc(m);
-    if (mo) break;
+    if (mo) {
+      if (first_opq) *first_opq = i0 - lo + __ffs(mo);
+      break;
+    }
   }
   return cnt;
 }
@@ -1168,7 +1186,7 @@ __global__ void __launch_bounds__(32 * GN_RAYS_PER_BLOCK)
 k_cand_count(const ObjState* __restrict__ st, const int* __restrict__ ray_obj, const int* __restrict__ ray_base,
              const int* __restrict__ ray_nev, int R, const float* __restrict__ q_sdf, int* __restrict__ cand_cnt,
              int* __restrict__ blk_tot, int* __restrict__ blk_base, int* __restrict__ band_base_end,
-             int* __restrict__ counters, int M, int cap) {
+             int* __restrict__ counters, int M, int cap, int* __restrict__ ray_hint) {
   pdl_prologue();
   __shared__ int s_cnt[GN_RAYS_PER_BLOCK];
   __shared__ int s_last;
@@ -1177,8 +1195,12 @@ k_cand_count(const ObjState* __restrict__ st, const int* __restrict__ ray_obj, c
   int cnt = 0;
   if (r < R) {
     const int lo = ray_base[r];
-    cnt = for_each_candidate(lo, lo + ray_nev[r], st[ray_obj[r]].cand_lim, q_sdf, lane, [](int, int) {});
-    if (lane == 0) cand_cnt[r] = cnt;
+    int first_opq;
+    cnt = for_each_candidate(lo, lo + ray_nev[r], st[ray_obj[r]].cand_lim, q_sdf, lane, [](int, int) {}, &first_opq);
+    if (lane == 0) {
+      cand_cnt[r] = cnt;
+      if (ray_hint) ray_hint[r] = first_opq;              // k_phase_list's phase-0 length in the next GN iteration
+    }
   }
   if (lane == 0) s_cnt[warp] = cnt;
   __syncthreads();

@@ -90,6 +90,52 @@ def test_fused_sequence_is_bit_identical_to_the_unfused_one(golden, decoder_stat
                 np.testing.assert_array_equal(a[k], b[k])
 
 
+@pytest.mark.parametrize("style,samples,slack", [("kitti", 50, None), ("redwood", 100, "0"), ("redwood", 72, "3")])
+def test_hinted_first_pass_runs_are_bit_identical_to_fixed_runs(golden, decoder_state, style, samples, slack):
+    """Phase 0 of the first pass decodes, per ray, the previous iteration's first-opaque position + slack samples
+    (QSP_HINT=0: runs of 32).  How a ray is cut into runs cannot change a result - only how many samples behind the
+    first opaque one are decoded: records, per-iteration H / b / dx and index lists agree bit for bit over ten
+    iterations (ragged batch with a failing member), and from iteration 1 on fewer rows go through the first pass."""
+    far = golden["redwood0_rays"].copy()
+    far[:, 0] += 5.0
+    dets = _dets(golden, ["kitti0", "redwood1", "kitti1", "redwood0"])
+    dets.insert(1, dict(t_cam_obj=golden["redwood0_t_cam_obj"], pts=golden["redwood0_pts"][:77], rays=far,
+                        depth=golden["redwood0_depth"]))
+    outs = []
+    for hint in ("1", "0"):
+        d = _decoder_with_env(decoder_state, QSP_HINT=hint, QSP_HINT_SLACK=slack if hint == "1" else None)
+        opt = make_opt(d, style, 10, samples=samples)
+        opt.set_debug(True)
+        rec = opt.reconstruct_objects_records(dets)
+        its = [[opt.get_iteration(i, b) for b in range(len(dets))] for i in range(10)]
+        opt.set_debug(False)
+        rec_fast = opt.reconstruct_objects_records(dets)              # and without the per-iteration syncs of debug mode
+        outs.append((rec, its, rec_fast))
+        d.close()
+    (r1, i1, f1), (r0, i0, f0) = outs
+    assert [bool(x) for x in r1[:, 80]] == [True, False, True, True, True]
+    np.testing.assert_array_equal(r1, r0)
+    np.testing.assert_array_equal(f1, r1)
+    np.testing.assert_array_equal(f0, r0)
+    rows1 = rows0 = 0
+    for e, (a_it, b_it) in enumerate(zip(i1, i0)):
+        for a, b in zip(a_it, b_it):
+            if a["failed"]:
+                assert b["failed"]
+                continue
+            for k in ("n_inball", "n_band", "n_keep", "n_cand"):
+                assert a[k] == b[k], k
+            for k in ("keep_ray", "keep_sample", "H", "b", "dx"):
+                np.testing.assert_array_equal(a[k], b[k])
+            if e == 0:
+                assert a["n_first_pass"] == b["n_first_pass"]          # no hint yet
+            else:
+                rows1 += a["n_first_pass"]
+                rows0 += b["n_first_pass"]
+    assert rows1 < rows0
+    print(f"first-pass rows, iterations 1-9: hinted {rows1}, fixed {rows0} ({rows1 / rows0:.3f})")
+
+
 @pytest.mark.parametrize("name,style,samples", [("kitti0", "kitti", 50), ("redwood1", "redwood", 72)])
 def test_side_stream_surface_rows_are_bit_identical(golden, decoder_state, name, style, samples):
     """Small batches: the surface rows' fwd+Jacobian launch runs on the handle's side stream next to the first pass
