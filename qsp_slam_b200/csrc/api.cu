@@ -116,6 +116,8 @@ struct qsp_decoder {
   bool phases = true;                              // first pass front to back in phases of 32 samples per ray
   bool hint = true;                                // phase 0 sized per ray from the previous iteration's first opaque sample
   int hint_slack = 1;                              // samples decoded beyond that position
+  int hint_mid = 8;                                // run length of a hinted iteration's middle phase
+  int surf_rounds = 0;                             // tiles per CTA of the side-stream surface launch (0: estimated)
   int pre_reduce = -1;                             // QSP_REDUCE=0/1: k_reduce_partials before k_solve (default: when >= 8 chunks)
   bool timeline = false;                           // QSP_TIMELINE=1: CUDA-event time of every launch group of one GN iteration
   bool fused = true;                               // QSP_FUSED=0: the unfused small-kernel sequence (A/B, bit-identical results)
@@ -397,6 +399,8 @@ extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_
   if (const char* e = getenv("QSP_PHASES")) d->phases = atoi(e) != 0;
   if (const char* e = getenv("QSP_HINT")) d->hint = atoi(e) != 0;
   if (const char* e = getenv("QSP_HINT_SLACK")) d->hint_slack = std::max(0, atoi(e));
+  if (const char* e = getenv("QSP_HINT_MID")) d->hint_mid = std::max(1, atoi(e));
+  if (const char* e = getenv("QSP_SURF_ROUNDS")) d->surf_rounds = std::max(0, atoi(e));
   if (const char* e = getenv("QSP_TIMELINE")) d->timeline = atoi(e) != 0;
   if (const char* e = getenv("QSP_REDUCE")) d->pre_reduce = atoi(e) != 0;
   if (const char* e = getenv("QSP_FUSED")) d->fused = atoi(e) != 0;
@@ -870,7 +874,28 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
   const long first_tiles_max = ((long)R * S + 127) / 128;
   const bool conc = d->concurrent && d->fused && hp_mode == DEC_SPLIT && !d->debug && !d->timeline && M > 0 &&
                     4 * surf_tiles <= d->num_sms && first_tiles_max <= 8L * d->num_sms;
-  const int surf_grid = (surf_tiles + 1) / 2 * 2;
+  // How many tiles each CTA of the side launch walks (k rounds of ~136 us on ceil(tiles / k) SMs): more rounds leave
+  // more SMs to the first pass as long as the side launch still ends before k_accumulate needs its rows, i.e. within
+  // the first pass plus the candidates' own fwd+Jacobian round.  Estimated from the call's sizes (about 45 % of the
+  // R x S samples are decoded; round times of the two persistent kernels measured on kitti_single: 49 / 136 us);
+  // QSP_SURF_ROUNDS=k forces k.
+  int surf_rounds = 1;
+  if (conc) {
+    if (d->surf_rounds > 0) {
+      surf_rounds = d->surf_rounds;
+    } else {
+      const double t_f = 49.0, t_j = 136.0, est_rows = 0.45 * (double)R * S;
+      double best = 1e30;
+      for (int k = 1; k <= 4; ++k) {
+        const int g = d->pair_grid - 2 * (((surf_tiles + 1) / 2 + k - 1) / k);
+        if (g < 2) continue;
+        const double t_first = std::ceil(est_rows / (g / 2 * 256.0)) * t_f + (n_phases - 1) * t_f;
+        if (k > 1 && k * t_j > t_first + t_j) break;
+        if (t_first < best - 1e-9) { best = t_first; surf_rounds = k; }
+      }
+    }
+  }
+  const int surf_grid = 2 * (((surf_tiles + 1) / 2 + surf_rounds - 1) / surf_rounds);
   const int first_grid_cap = conc ? std::max(2, d->pair_grid - surf_grid) : 0;
   std::vector<std::pair<const char*, cudaEvent_t>> marks;   // diagnostic timeline of the last iteration
 #define MARK(name)                                                        \
@@ -906,9 +931,11 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
     // (a) forward decode of the in-ball samples (loss.py:77-78), first pass
     // in phases of 32 samples along the ray; a ray stops at its first certainly-opaque sample (k_phase_list)
     if (d->phases) {
-      for (int ph = 0; ph < n_phases; ++ph) {
-        KL(k_phase_list, ray_blocks, tb, st, ph, (int)(ph == n_phases - 1), R, state, ray_obj, ray_base, ray_cnt, q_sdf, q_code, ray_nev, ray_prev,
-           (const int*)(use_hint && it > 0 ? ray_hint : nullptr), d->hint_slack, ph_list, ph_code, phase_cnt);
+      const bool hinted = use_hint && it > 0;
+      const int n_ph_it = hinted ? std::min(n_phases, 3) : n_phases;
+      for (int ph = 0; ph < n_ph_it; ++ph) {
+        KL(k_phase_list, ray_blocks, tb, st, ph, (int)(ph == n_ph_it - 1), R, state, ray_obj, ray_base, ray_cnt, q_sdf, q_code, ray_nev, ray_prev,
+           (const int*)(hinted ? ray_hint : nullptr), d->hint_slack, hinted ? d->hint_mid : 32, ph_list, ph_code, phase_cnt);
         MARK("k_phase_list");
         if ((r = launch_decoder(d, first_mode, false, q_pts, ph_code, codes_dev, code_stride, 0, phase_cnt + ph, 1, q_sdf, nullptr, st, ph_list, first_grid_cap))) return r;
         MARK("first-pass decoder");

@@ -262,6 +262,8 @@ __global__ void k_sample_fused(const ObjState* __restrict__ st, const float* __r
 // own).  With a hint (ray_hint[r] = position of the ray's first opaque sample in the PREVIOUS GN iteration, written
 // by the candidate kernels; the whole ray when it had none) phase 0 decodes hint + slack samples instead: the pose
 // moves little between iterations, so most rays end inside phase 0 with `slack` wasted samples rather than ~16.
+// A ray that misses its hint mostly misses it by a few samples (scripts/phase_schedule_sim.py), so hinted iterations
+// run at most three phases: hint + slack, mid_len = 8, the rest.
 #define GN_PHASE_TAIL 8
 __host__ __device__ inline int gn_num_phases(int S) {
   const int full = (S + 31) / 32, rem = S - (full - 1) * 32;
@@ -270,7 +272,7 @@ __host__ __device__ inline int gn_num_phases(int S) {
 __global__ void k_phase_list(int p, int last, int R, const ObjState* __restrict__ st, const int* __restrict__ ray_obj,
                              const int* __restrict__ ray_base, const int* __restrict__ ray_cnt, const float* __restrict__ q_sdf,
                              const int* __restrict__ q_code, int* __restrict__ ray_nev, int* __restrict__ ray_prev,
-                             const int* __restrict__ ray_hint, int slack,
+                             const int* __restrict__ ray_hint, int slack, int mid_len,
                              int* __restrict__ list, int* __restrict__ list_code, int* __restrict__ phase_cnt) {
   pdl_prologue();
   int r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
@@ -288,7 +290,7 @@ __global__ void k_phase_list(int p, int last, int R, const ObjState* __restrict_
     if (__any_sync(0xffffffffu, opq)) return;
   }
   if (start >= n) return;
-  const int len = last ? n - start : (p == 0 && ray_hint) ? ray_hint[r] + slack : 32;
+  const int len = last ? n - start : (p == 0 && ray_hint) ? ray_hint[r] + slack : mid_len;
   const int m = min(len, n - start);
   int base = 0;
   if (lane == 0) base = atomicAdd(phase_cnt + p, m);
