@@ -95,8 +95,10 @@ def read_ply(path: str):
 def extract_map_objects(map_dir: str, extractors, default_class: int = 0) -> List[int]:
     """The body of extract_map_objects.py:40-61 / extract_map_objects_multi.py:74-98: for every object of
     ``<map_dir>/MapObjects.txt`` save ``objects/<id>.npy`` (4x4 pose) and ``objects/<id>.ply`` (mesh of its code).
-    ``extractors``: one MeshExtractor, or a dict class id -> MeshExtractor.  All grids of a class are decoded by ONE
-    launch of the decoder kernel per batch (BASELINE config 4) before the per-object isosurface extraction."""
+    ``extractors``: one MeshExtractor, or a dict class id -> MeshExtractor.  One native call per object
+    (qsp_extract_mesh: first-pass grid decode, exact re-evaluation of the cells near the level set, isosurface
+    kernels; only vertices and faces come back).  The many-grids-in-one-launch form of BASELINE config 4 is
+    ``MeshExtractor.decode_grid(codes)`` / bench.py's ``mesh_grid_128x64``, which decodes full grids and is not needed for the meshes."""
     save_dir = os.path.join(map_dir, "objects")
     os.makedirs(save_dir, exist_ok=True)
     objs = read_map_objects(os.path.join(map_dir, "MapObjects.txt"))

@@ -3,11 +3,16 @@ surface, against (1) the committed outputs of the unmodified reference (tests/go
 oracle on the same seeded inputs.  Tolerances (BASELINE.json north_star): per-point SDF <= 1e-3
 absolute (we hold 2e-5 on the exact-fp32 path), pose/code <= 1e-3 relative per iteration, identical
 ray/sample index sets."""
+import json
+import os
+
 import numpy as np
 import pytest
 import torch
 
 from qsp_slam_b200 import synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 pytestmark = pytest.mark.gpu
 
@@ -640,6 +645,7 @@ def test_random_objects_index_sets_vs_oracle(dev, decoder_state, orc, style, wor
         opt.set_debug(False)
     prm = G.Params(cfg)
     n_keep = n_good = 0
+    errs = []
     for o, z, r, it in zip(objs, codes, res, its):
         t_oc = torch.inverse(torch.from_numpy(o["t_cam_obj"].copy()))
         ref = G.gn_iteration(fd, prm, t_oc, torch.from_numpy(z), torch.from_numpy(np.ascontiguousarray(o["pts"])),
@@ -661,5 +667,16 @@ def test_random_objects_index_sets_vs_oracle(dev, decoder_state, orc, style, wor
         # 200 surface points and a few dozen band rows: one ReLU flip in a band row moves b by ~5e-4, and the KITTI
         # system (k4 = 1e7 on the rotation block) amplifies it several-fold on dx
         # (observed up to 1.2e-2 on an object with three kept band rows; b itself holds 1e-3)
-        assert np.abs(it["dx"] - dref).max() < 1e-1 * np.abs(dref).max()
+        e_dx = float(np.abs(it["dx"] - dref).max() / np.abs(dref).max())
+        e_b = float(np.abs(it["b"] - bref).max() / np.abs(bref).max())
+        assert e_dx < 1e-1
+        errs.append((e_b, e_dx, int(it["n_keep"])))
     assert n_good >= 8 and n_keep > 100
+    # the hard bounds above admit single flips; the bulk must sit far below them (a moderate numeric regression moves
+    # every object, a flip moves one)
+    e = np.array(errs)
+    out = os.path.join(ROOT, "gpurun_out")
+    os.makedirs(out, exist_ok=True)
+    with open(os.path.join(out, "random_objects_errors.jsonl"), "a") as f:
+        f.write(json.dumps({"workload": workload, "b": e[:, 0].tolist(), "dx": e[:, 1].tolist(), "n_keep": e[:, 2].tolist()}) + "\n")
+    assert np.median(e[:, 0]) < 1e-3 and np.median(e[:, 1]) < 5e-3
