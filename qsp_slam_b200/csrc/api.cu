@@ -116,6 +116,7 @@ struct qsp_decoder {
   bool phases = true;                              // first pass front to back in phases of 32 samples per ray
   bool hint = true;                                // phase 0 sized per ray from the previous iteration's first opaque sample
   int hint_slack = 1;                              // samples decoded beyond that position
+  int hint_phases = 3;                             // phases of a hinted iteration: hint + slack, (mid,) rest
   int hint_mid = 8;                                // run length of a hinted iteration's middle phase
   int surf_rounds = 0;                             // tiles per CTA of the side-stream surface launch (0: estimated)
   int pre_reduce = -1;                             // QSP_REDUCE=0/1: k_reduce_partials before k_solve (default: when >= 8 chunks)
@@ -399,6 +400,13 @@ extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_
   if (const char* e = getenv("QSP_PHASES")) d->phases = atoi(e) != 0;
   if (const char* e = getenv("QSP_HINT")) d->hint = atoi(e) != 0;
   if (const char* e = getenv("QSP_HINT_SLACK")) d->hint_slack = std::max(0, atoi(e));
+#ifdef QSP_EXPERIMENTAL
+  if (const char* e = getenv("QSP_SOLVE_PROFILE")) {
+    const int on = atoi(e) != 0;
+    cudaMemcpyToSymbol(g_solve_profile, &on, sizeof(int));
+  }
+#endif
+  if (const char* e = getenv("QSP_HINT_PHASES")) d->hint_phases = std::min(std::max(2, atoi(e)), GN_MAXC);
   if (const char* e = getenv("QSP_HINT_MID")) d->hint_mid = std::max(1, atoi(e));
   if (const char* e = getenv("QSP_SURF_ROUNDS")) d->surf_rounds = std::max(0, atoi(e));
   if (const char* e = getenv("QSP_TIMELINE")) d->timeline = atoi(e) != 0;
@@ -932,7 +940,7 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
     // in phases of 32 samples along the ray; a ray stops at its first certainly-opaque sample (k_phase_list)
     if (d->phases) {
       const bool hinted = use_hint && it > 0;
-      const int n_ph_it = hinted ? std::min(n_phases, 3) : n_phases;
+      const int n_ph_it = hinted ? std::min(n_phases, d->hint_phases) : n_phases;
       for (int ph = 0; ph < n_ph_it; ++ph) {
         KL(k_phase_list, ray_blocks, tb, st, ph, (int)(ph == n_ph_it - 1), R, state, ray_obj, ray_base, ray_cnt, q_sdf, q_code, ray_nev, ray_prev,
            (const int*)(hinted ? ray_hint : nullptr), d->hint_slack, hinted ? d->hint_mid : 32, ph_list, ph_code, phase_cnt);

@@ -785,6 +785,13 @@ k_reduce_partials(const float* __restrict__ partials, int nchunk, int pose_only,
 // H is SPD after damping so the solutions agree to rounding), exp map and state update (:261-263).
 // One CTA per object.  `ndof` = 71 (joint) or 6 (pose only, optimizer.py:72-78).
 // ------------------------------------------------------------------------------------------------
+#ifdef QSP_EXPERIMENTAL
+// cycle profile of k_solve's stages (thread 0 of object 0; QSP_SOLVE_PROFILE=1, experimental build only)
+__device__ int g_solve_profile = 0;
+#define SOLVE_T(i) do { if (prof) tprof[i] = clock64(); } while (0)
+#else
+#define SOLVE_T(i) do { } while (0)
+#endif
 __global__ void __launch_bounds__(256)
 k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
         const float* __restrict__ partials, GnParamsDev p, int pose_only,
@@ -795,6 +802,11 @@ k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
   __shared__ float dxs[72];
   __shared__ int fail_s;
   const int o = blockIdx.x, tid = threadIdx.x;
+#ifdef QSP_EXPERIMENTAL
+  const bool prof = g_solve_profile && o == 0 && tid == 0;
+  long long tprof[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#endif
+  SOLVE_T(0);
   ObjState& s = st[o];
   if (s.failed) return;
   const int M = m_active ? m_active[o] : pts_off[o + 1] - pts_off[o], P = s.n_keep, Q = s.n_inball;
@@ -835,19 +847,40 @@ k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
       }
     }
 #pragma unroll
+    SOLVE_T(1);
+    // scale, add the regulariser / rotation prior / damping (same float operations in the same order as the
+    // reference's H, optimizer.py:232-252) and store both halves; row / column 71 ([J r]^T r and r^T r) stays raw
+    float jr[3] = {0.f, 0.f, 0.f};
+    if (!pose_only) { jr[0] = s.J_rot[0]; jr[1] = s.J_rot[1]; jr[2] = s.J_rot[2]; }
+#pragma unroll
     for (int k = 0; k < EPT; ++k) {
       const int e = tid + k * 256;
       if (e < NE) {
-        int i = 0, r = e;
-        while (r >= 72 - i) { r -= 72 - i; ++i; }
-        const int j = i + r;
+        // entry e of the row-major upper triangle: row i starts at i * 72 - i (i - 1) / 2
+        int i = (int)((145.f - sqrtf(21025.f - 8.f * (float)e)) * 0.5f);
+        i = min(max(i, 0), 71);
+        int off = i * 72 - (i * (i - 1)) / 2;
+        if (off > e) { --i; off = i * 72 - (i * (i - 1)) / 2; }
+        else if (e - off >= 72 - i) { off += 72 - i; ++i; }
+        const int j = i + (e - off);
         const float v = pose_only ? ss[k] / (float)M : wr * sr[k] / (float)P + ws * ss[k] / (float)M;
-        A[i][j] = (double)v;                              // fp32 values, held exactly
-        A[j][i] = (double)v;
+        float h = v;
+        if (j < 71) {
+          if (pose_only) { if (i == j) h += 1e-2f; }                           // optimizer.py:74
+          else {
+            if (i == j && i >= 7) h += p.k3;                                   // :232
+            if (i >= 3 && i < 6 && j >= 3 && j < 6) h += p.k4 * (jr[i - 3] * jr[j - 3]);  // :241,243
+            if (i == j && i < 7) h += 1.0f;                                    // :251
+            if (i == 6 && j == 6) h += p.s_damp;                               // :252
+          }
+        }
+        A[i][j] = (double)h;                              // fp32 values, held exactly
+        A[j][i] = (double)h;
       }
     }
   }
   __syncthreads();
+  SOLVE_T(2);
   if (tid == 0) {
     float loss = (float)A[71][71];                            // k1*render_loss + k2*sdf_loss (optimizer.py:205)
     int f = 0;
@@ -858,7 +891,7 @@ k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
   }
   __syncthreads();
   if (fail_s) return;
-  // b = -J^T r ; regulariser, rotation prior, damping
+  // b = -J^T r ; regulariser, rotation prior
   if (tid < n) {
     float b = -(float)A[tid][71];
     if (!pose_only) {
@@ -867,20 +900,12 @@ k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
     }
     rhs[tid] = (double)b;
   }
-  __syncthreads();
-  for (int v = tid; v < n * n; v += blockDim.x) {
-    int i = v / n, j = v - i * n;
-    float h = (float)A[i][j];
-    if (pose_only) { if (i == j) h += 1e-2f; }                           // optimizer.py:74
-    else {
-      if (i == j && i >= 7) h += p.k3;                                   // :232
-      if (i >= 3 && i < 6 && j >= 3 && j < 6) h += p.k4 * (s.J_rot[i - 3] * s.J_rot[j - 3]);  // :241,243
-      if (i == j && i < 7) h += 1.0f;                                    // :251
-      if (i == 6 && j == 6) h += p.s_damp;                               // :252
+  if (dbg_H)
+    for (int v = tid; v < n * n; v += blockDim.x) {
+      const int i = v / n, j = v - i * n;
+      dbg_H[(size_t)o * 71 * 71 + i * 71 + j] = (float)A[i][j];
     }
-    A[i][j] = (double)h;
-    if (dbg_H) dbg_H[(size_t)o * 71 * 71 + i * 71 + j] = h;
-  }
+  __syncthreads();
   if (dbg_b && tid < n) dbg_b[o * 71 + tid] = (float)rhs[tid];
   __syncthreads();
   // Cholesky A = L L^T (lower), fp64, with the right-hand side carried as row n of the lower triangle (forward
@@ -889,6 +914,7 @@ k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
   // L_ik = A[i][k] * rhs[k] and y_k = A[n][k] * rhs[k].
   if (tid < n) A[n][tid] = rhs[tid];
   __syncthreads();
+  SOLVE_T(3);
   {
     // Thread (ti, tj) of a 16 x 16 arrangement keeps its elements A[ti + 16a][tj + 16b], b <= a, of the working
     // matrix in registers; smem holds the finished (unscaled) columns.  Step k: the owners of column k publish it
@@ -934,6 +960,7 @@ k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
     }
     __syncthreads();
   }
+  SOLVE_T(4);
   // back substitution L^T x = y by one warp, column oriented, y in registers (lane owns entries lane, lane + 32,
   // lane + 64): x_i = y_i / L_ii, then y_j -= L_ij x_i for j < i, with L_ij = A[i][j] * rhs[j], L_ii = 1 / rhs[i]
   if (tid < 32) {
@@ -960,6 +987,7 @@ k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
       if (tid + 32 * u < n) A[n][tid + 32 * u] = y[u];
   }
   __syncthreads();
+  SOLVE_T(5);
   if (tid < n) rhs[tid] = A[n][tid];
   __syncthreads();
   if (tid < n) {
@@ -980,6 +1008,12 @@ k_solve(ObjState* __restrict__ st, const int* __restrict__ pts_off, int nchunk,
       }
     for (int i = 0; i < 16; ++i) s.T_oc[i] = N[i];                                 // optimizer.py:262
   }
+#ifdef QSP_EXPERIMENTAL
+  SOLVE_T(6);
+  if (prof)
+    printf("k_solve cycles: load+sum %lld, assemble %lld, loss/b/H %lld, cholesky %lld, back-subst %lld, update %lld\n",
+           tprof[1] - tprof[0], tprof[2] - tprof[1], tprof[3] - tprof[2], tprof[4] - tprof[3], tprof[5] - tprof[4], tprof[6] - tprof[5]);
+#endif
 }
 
 // records: t_cam_obj (16) | code (64) | is_good | loss  (optimizer.py:274-281)
