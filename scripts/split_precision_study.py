@@ -10,7 +10,7 @@ torch.set_num_threads(8)
 st = synth.make_decoder_state(0)
 fd = G.FoldedDecoder(st, torch.float64)
 rng = np.random.default_rng(5)
-n = 20000
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 20000
 x = torch.from_numpy(synth._ball_points(rng, n)).double()
 z = torch.from_numpy((rng.standard_normal(64) * 0.1).astype(np.float32)).double()
 s_ref, g_ref = G.decoder_forward_jacobian(fd, z, x)
