@@ -413,6 +413,22 @@ def main():
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e = world * B * n_e2e / float(te.item())
 
+    # per rank: rounds of the dominant kernel summed over the iterations of one step (k_decoder_p3 walks
+    # ceil(tiles / SMs) rounds of equal length: a share with slightly more candidate rows crosses into another round)
+    opt.set_debug(True)
+    opt.reconstruct_objects(objs)
+    n_it = cfg["optimizer"]["joint_optim"]["num_iterations"]
+    m_rows = sum(o["pts"].shape[0] for o in objs)
+    sms = torch.cuda.get_device_properties(local_rank).multi_processor_count
+    jac_rows = [m_rows + sum(opt.get_iteration(i, b)["n_cand"] for b in range(B)) for i in range(n_it)]
+    opt.set_debug(False)
+    jac_rounds = sum(-(-(-(-r // 64)) // sms) for r in jac_rows)
+    tr = torch.tensor([float(jac_rounds), float(sum(jac_rows))], dtype=torch.float64, device="cuda")
+    trmax, trmin = tr.clone(), tr.clone()
+    if world > 1:
+        dist.all_reduce(trmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(trmin, op=dist.ReduceOp.MIN)
+
     # BASELINE config 5 next to the weak-scaling headline: a fixed map of `map_objects` objects, STRONG scaling
     map_scale = None
     if world > 1 and args.map_objects > 0:
@@ -536,8 +552,11 @@ def main():
                "ranks": {"timed_region_ms": {"max": float(tmax[0]), "min": float(tmin[0])},
                          "compute_ms_sum": {"max": float(tmax[1]), "min": float(tmin[1])},
                          "gather_tail_ms_sum": {"max": float(tmax[2]), "min": float(tmin[2])},
+                         "fwd_jac_rounds_per_step": {"max": int(trmax[0]), "min": int(trmin[0])},
+                         "fwd_jac_rows_per_step": {"max": int(trmax[1]), "min": int(trmin[1])},
                          "note": "per rank: whole timed region; sum over steps of the GN solve; sum over steps of "
-                                 "(gather end - solve end) on the side stream"},
+                                 "(gather end - solve end) on the side stream; rounds (ceil(tiles / SMs), summed over the "
+                                 "iterations of one step) and rows of the fwd+Jacobian launch"},
                "map_scale": map_scale,
                "decoder_evals_per_s": {k: v["evals_per_s"] for k, v in kern.items()},
                "rows_per_iteration": {"in_ball_samples": sum(i["n_inball"] for i in its), "first_pass": q_rows,

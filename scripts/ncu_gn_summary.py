@@ -54,7 +54,7 @@ for r in rows[2:]:
 out = os.path.join(root, "profiles", f"{tag}_ncu_gn_kernels_summary.txt")
 with open(out, "w") as f:
     f.write("# ncu --set full --clock-control none, the Gauss-Newton kernels (b)-(d) of one warm kitti_batch32 iteration\n"
-            "# (python bench.py --steps 1 --warmup 1 --no-cpu-baseline, launches of the second step).  Per launch averages;\n"
+            "# (QSP_TIMELINE=0 python scripts/timeline.py, launches 120.. of the run: a warm step).  Per launch averages;\n"
             f"# GB/s = (dram__bytes_read.sum + dram__bytes_write.sum) / gpu__time_duration.sum; HBM peak {peak:.0f} GB/s (measured copy).\n"
             "# Under ncu every launch is cold-cache and serialised: the byte counts are the evidence, the times are upper bounds.\n")
     f.write(f"{'kernel':28s} {'n':>3s} {'us':>8s} {'rd KB':>9s} {'wr KB':>9s} {'GB/s':>8s} {'%HBM':>6s} {'dram%':>6s} {'L2%':>6s} "

@@ -13,7 +13,8 @@ for src, dst in (("launches.csv", "launches_bench.csv"), ("bench.json", "bench.j
                  ("fullsize_parity.jsonl", "fullsize_parity.jsonl"), ("fullsize_parity_cases.jsonl", "fullsize_parity_cases.jsonl"),
                  ("bench_gpus2.json", "bench_gpus2.json"), ("bench_gpus4.json", "bench_gpus4.json"),
                  ("bench_gpus8.json", "bench_gpus8.json"), ("bench_gpus1_samebox.json", "bench_gpus1_samebox.json"),
-                 ("pytest_gpu_tail.txt", "pytest_gpu_tail.txt"), ("smi.txt", "smi.txt")):
+                 ("pytest_gpu_tail.txt", "pytest_gpu_tail.txt"), ("smi.txt", "smi.txt"),
+                 ("launches_kitti_single.csv", "launches_kitti_single.csv"), ("random_objects_errors.jsonl", "random_objects_errors.jsonl")):
     if os.path.exists(os.path.join(go, src)):
         shutil.copy(os.path.join(go, src), os.path.join(pr, f"{tag}_{dst}"))
 bench = json.load(open(os.path.join(go, "bench.json")))

@@ -1,7 +1,7 @@
 """In-situ CUDA-event timeline of one GN iteration of kitti_batch32 (QSP_TIMELINE=1): where the time outside the
 two decoder kernels goes.  Prints the library's stderr lines of a warm step."""
 import os, sys
-os.environ["QSP_TIMELINE"] = "1"
+os.environ.setdefault("QSP_TIMELINE", "1")      # QSP_TIMELINE=0: the same calls without per-kernel events (ncu passes)
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np
 from qsp_slam_b200 import synth
