@@ -118,6 +118,7 @@ struct qsp_decoder {
   int hint_slack = 1;                              // samples decoded beyond that position
   int hint_phases = 3;                             // phases of a hinted iteration: hint + slack, (mid,) rest
   int hint_mid = 8;                                // run length of a hinted iteration's middle phase
+  int tail_side = 48;                              // SMs of the surface-row launch that runs beside the tail phases (0: off)
   int surf_rounds = 0;                             // tiles per CTA of the side-stream surface launch (0: estimated)
   int pre_reduce = -1;                             // QSP_REDUCE=0/1: k_reduce_partials before k_solve (default: when >= 8 chunks)
   bool timeline = false;                           // QSP_TIMELINE=1: CUDA-event time of every launch group of one GN iteration
@@ -125,7 +126,7 @@ struct qsp_decoder {
   bool concurrent = true;                          // QSP_CONCURRENT=0: never split the surface rows onto the side stream
   long band_cap = 0;                               // QSP_BAND_CAP=n (debug): candidate row capacity, to exercise the overflow path
   cudaStream_t side = nullptr;                     // surface-row decoder launch of small batches, concurrent with the first pass
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_x = nullptr;
   // diagnostics of the last qsp_reconstruct_batch call: candidate overflow flag, max |first pass - exact| (float
   // bits), candidates whose first-pass error exceeded 3/4 of the margin; valid once the call has been synchronised
   int last_stats[3] = {0, 0, 0};
@@ -408,6 +409,7 @@ extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_
 #endif
   if (const char* e = getenv("QSP_HINT_PHASES")) d->hint_phases = std::min(std::max(2, atoi(e)), GN_MAXC);
   if (const char* e = getenv("QSP_HINT_MID")) d->hint_mid = std::max(1, atoi(e));
+  if (const char* e = getenv("QSP_TAIL_SIDE")) d->tail_side = std::max(0, atoi(e)) & ~1;
   if (const char* e = getenv("QSP_SURF_ROUNDS")) d->surf_rounds = std::max(0, atoi(e));
   if (const char* e = getenv("QSP_TIMELINE")) d->timeline = atoi(e) != 0;
   if (const char* e = getenv("QSP_REDUCE")) d->pre_reduce = atoi(e) != 0;
@@ -423,6 +425,7 @@ extern "C" int qsp_decoder_create(const qsp_decoder_weights* w, int device, qsp_
   CK(cudaStreamCreateWithFlags(&d->side, cudaStreamNonBlocking));
   CK(cudaEventCreateWithFlags(&d->ev_fork, cudaEventDisableTiming));
   CK(cudaEventCreateWithFlags(&d->ev_join, cudaEventDisableTiming));
+  CK(cudaEventCreateWithFlags(&d->ev_x, cudaEventDisableTiming));
   *out = d;
   return QSP_OK;
 }
@@ -495,6 +498,7 @@ extern "C" void qsp_decoder_destroy(qsp_decoder* d) {
   if (d->ev1) cudaEventDestroy(d->ev1);
   if (d->ev_fork) cudaEventDestroy(d->ev_fork);
   if (d->ev_join) cudaEventDestroy(d->ev_join);
+  if (d->ev_x) cudaEventDestroy(d->ev_x);
   if (d->side) cudaStreamDestroy(d->side);
   delete d;
 }
@@ -905,6 +909,10 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
   }
   const int surf_grid = 2 * (((surf_tiles + 1) / 2 + surf_rounds - 1) / surf_rounds);
   const int first_grid_cap = conc ? std::max(2, d->pair_grid - surf_grid) : 0;
+  // see the phase loop: surface tiles that run beside the tail phases of hinted iterations (batch path only)
+  const bool tail_ok = !conc && d->tail_side > 0 && d->fused && d->phases && hp_mode == DEC_SPLIT && first_mode == DEC_FAST &&
+                       !d->debug && !d->timeline && d->tail_side <= d->pair_grid / 2 && (long)M >= 4L * d->tail_side * 64;
+  long tail_rows = 0;
   std::vector<std::pair<const char*, cudaEvent_t>> marks;   // diagnostic timeline of the last iteration
 #define MARK(name)                                                        \
   do {                                                                    \
@@ -941,12 +949,27 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
     if (d->phases) {
       const bool hinted = use_hint && it > 0;
       const int n_ph_it = hinted ? std::min(n_phases, d->hint_phases) : n_phases;
+      tail_rows = (tail_ok && hinted && n_ph_it >= 2) ? (long)d->tail_side * 64 : 0;
       for (int ph = 0; ph < n_ph_it; ++ph) {
         KL(k_phase_list, ray_blocks, tb, st, ph, (int)(ph == n_ph_it - 1), R, state, ray_obj, ray_base, ray_cnt, q_sdf, q_code, ray_nev, ray_prev,
            (const int*)(hinted ? ray_hint : nullptr), d->hint_slack, hinted ? d->hint_mid : 32, ph_list, ph_code, phase_cnt);
         MARK("k_phase_list");
-        if ((r = launch_decoder(d, first_mode, false, q_pts, ph_code, codes_dev, code_stride, 0, phase_cnt + ph, 1, q_sdf, nullptr, st, ph_list, first_grid_cap))) return r;
+        if ((r = launch_decoder(d, first_mode, false, q_pts, ph_code, codes_dev, code_stride, 0, phase_cnt + ph, 1, q_sdf, nullptr, st, ph_list,
+                                (tail_rows > 0 && ph > 0) ? d->pair_grid - d->tail_side : first_grid_cap))) return r;
         MARK("first-pass decoder");
+        if (tail_rows > 0 && ph == 0) {
+          // Large batches, hinted iterations: the tail phases hold few rows (one round on a fraction of the SMs), so
+          // the first `tail_side` tiles of the SURFACE rows - known up front - run their fwd+Jacobian round beside them
+          // on the side stream, on SMs the tail phases leave idle; the main fwd+Jacobian launch below starts at row
+          // tail_rows.  k_decoder_p3 walks ceil(tiles / SMs) rounds of equal length, so a launch a few tiles beyond a
+          // multiple of the SM count loses a whole round: this takes tail_side tiles out of it for free.
+          CK(cudaEventRecord(d->ev_fork, st));
+          CK(cudaStreamWaitEvent(d->side, d->ev_fork, 0));
+          KL(k_surface_xform, std::max(1, (M + tb - 1) / tb), tb, d->side, state, in.pts, pt_obj, M, jp_pts, jp_code);
+          CK(cudaEventRecord(d->ev_x, d->side));
+          if ((r = launch_decoder(d, hp_mode, true, jp_pts, jp_code, codes_dev, code_stride, tail_rows, nullptr, 1, g_sdf, g_jac, d->side, nullptr, d->tail_side))) return r;
+          CK(cudaEventRecord(d->ev_join, d->side));
+        }
       }
     } else {
       if ((r = launch_decoder(d, first_mode, false, q_pts, q_code, codes_dev, code_stride, 0, counters + 0, 1, q_sdf, nullptr, st, nullptr, first_grid_cap))) return r;
@@ -955,7 +978,7 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
     // candidates near the band, appended behind the surface points in the Jacobian row list
     if (d->fused) {
       KL(k_cand_count, nblk, 32 * GN_RAYS_PER_BLOCK, st, state, ray_obj, ray_base, nev, R, q_sdf, band_cnt, blk_tot, blk_base,
-                                               band_base + R, counters, M, (int)bandcap, use_hint ? ray_hint : nullptr);
+                                               band_base + R, counters, M - (int)tail_rows, (int)bandcap, use_hint ? ray_hint : nullptr);
       KL(k_cand_fill, nblk, 32 * GN_RAYS_PER_BLOCK, st, state, ray_obj, ray_base, nev, R, q_sdf, band_cnt, blk_base, band_base, M,
                                               (int)bandcap, q_pts, q_code, q_samp, jp_pts, jp_code, row_ray, row_samp, cand_q, counters + 3);
     } else {
@@ -971,9 +994,15 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
       if ((r = launch_decoder(d, hp_mode, true, jp_pts + (size_t)M * 3, jp_code + M, codes_dev, code_stride, 0, counters + 7, 1,
                               g_sdf + M, g_jac + (size_t)M * QSP_JSTRIDE, st))) return r;
     } else {
-      KL(k_surface_xform, std::max(1, (M + tb - 1) / tb), tb, st, state, in.pts, pt_obj, M, jp_pts, jp_code);
-      MARK("candidates + k_surface_xform");
-      if ((r = launch_decoder(d, hp_mode, true, jp_pts, jp_code, codes_dev, code_stride, 0, counters + 2, 1, g_sdf, g_jac, st))) return r;
+      if (tail_rows > 0) {
+        CK(cudaStreamWaitEvent(st, d->ev_x, 0));               // the surface transform ran on the side stream
+        if ((r = launch_decoder(d, hp_mode, true, jp_pts + (size_t)tail_rows * 3, jp_code + tail_rows, codes_dev, code_stride, 0, counters + 2, 1,
+                                g_sdf + tail_rows, g_jac + (size_t)tail_rows * QSP_JSTRIDE, st))) return r;
+      } else {
+        KL(k_surface_xform, std::max(1, (M + tb - 1) / tb), tb, st, state, in.pts, pt_obj, M, jp_pts, jp_code);
+        MARK("candidates + k_surface_xform");
+        if ((r = launch_decoder(d, hp_mode, true, jp_pts, jp_code, codes_dev, code_stride, 0, counters + 2, 1, g_sdf, g_jac, st))) return r;
+      }
     }
     MARK("fwd+Jacobian decoder");
     // (b) occupancy, transmittance, rendered depth, band selection
@@ -991,7 +1020,7 @@ extern "C" int qsp_reconstruct_batch(qsp_decoder* d, const qsp_gn_params* prm, i
       MARK("k_refine_scatter + k_render + k_row_factors");
     }
     // (c) chain rule + normal equations, (d) solve + update
-    if (conc) CK(cudaStreamWaitEvent(st, d->ev_join, 0));      // the surface rows of the side stream
+    if (conc || tail_rows > 0) CK(cudaStreamWaitEvent(st, d->ev_join, 0));      // the surface rows of the side stream
     KL(k_accumulate, dim3(nchunk, B, 2), 256, st, state, d_pts_off, d_rays_off, band_base, M, jp_pts, g_sdf, g_jac,
                                                      row_fac, row_res, p.b2, p.b1, 0, nullptr, partials);
     MARK("k_accumulate");
