@@ -30,7 +30,7 @@ if [ "$MODE" = "full" ]; then
   QSP_TIMELINE=0 QSP_CALIBRATE=0 timeout 300 python scripts/timeline.py kitti_single > gpurun_out/plain_single.log 2>&1 &&
   QSP_TIMELINE=0 QSP_CALIBRATE=0 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 900 --csv --log-file gpurun_out/launches_kitti_single.csv \
     python scripts/timeline.py kitti_single > gpurun_out/ncu_single.log 2>&1; echo "ncu kitti_single launches rc=$?"
-  QSP_TIMELINE=0 QSP_CALIBRATE=0 timeout 900 ncu --set full --clock-control none -k regex:'^k_(prep|sample_fused|phase_list|cand_count|cand_fill|surface_xform|render|accumulate|reduce_partials|solve)' -s 120 -c 22 -o gpurun_out/gn_kernels -f \
+  [ -n "${QSP_ROUND_GN_NCU:-}" ] && QSP_TIMELINE=0 QSP_CALIBRATE=0 timeout 900 ncu --set full --clock-control none -k regex:'^k_(prep|sample_fused|phase_list|cand_count|cand_fill|surface_xform|render|accumulate|reduce_partials|solve)' -s 120 -c 22 -o gpurun_out/gn_kernels -f \
     python scripts/timeline.py > gpurun_out/ncu_gn.log 2>&1; echo "ncu gn kernels rc=$?"
 fi
 ls -la gpurun_out
