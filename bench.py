@@ -331,9 +331,11 @@ def main():
     # per-rank work is balanced; every rank generates the same list (seeded) and takes its share
     cfg, all_objs = synth.make_workload(WORKLOAD, state, objects=world * B, first_seed=1000, decode=decode)
     S = cfg["optimizer"]["num_depth_samples"]
-    shares = sharding.balanced_equal_counts([sharding.inball_cost(o, S) for o in all_objs], world)
+    proxy = [sharding.inball_cost(o, S) for o in all_objs]
+    shares = sharding.refine_equal_counts(proxy, sharding.balanced_equal_counts(proxy, world))
     objs = [all_objs[i] for i in shares[rank]]
     opt = Optimizer(dev, ForceKeyErrorDict(cfg))
+    balance = "equal counts by a host proxy (in-ball samples at the initial pose), refined by swaps"
     packed = opt.pack(objs)
     h2d = sum(packed[k].nbytes for k in ("T", "pts", "rays", "depth", "pts_off", "rays_off", "depth_off"))
     d2h = B * 82 * 4
@@ -541,6 +543,7 @@ def main():
             configs = other_configs(torch, dev, state, decode, pk)
         cfgd = workload_config(world, B)
         cfgd["good_objects"] = good
+        cfgd["shares"] = balance
         out = {"metric": METRIC, "value": value, "unit": "objects/s",
                "n_gpus": world, "steps": args.steps, "warmup": W,
                "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",

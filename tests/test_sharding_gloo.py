@@ -90,3 +90,22 @@ def test_gather_two_ranks_gloo():
         p.join(timeout=120)
         assert p.exitcode == 0
     assert got == [float(i) for i in range(n_obj)]
+
+
+def test_refined_equal_count_dealing_narrows_the_spread():
+    """refine_equal_counts: same number of objects per rank, every object dealt once, spread of the rank sums far below
+    the snake's (which is bounded by one object's cost only)."""
+    import numpy as np
+    from qsp_slam_b200 import sharding
+    rng = np.random.default_rng(3)
+    for world, per in ((8, 32), (4, 32), (2, 5), (3, 1)):
+        costs = (1.0 + 0.3 * rng.random(world * per)).tolist()
+        snake = sharding.balanced_equal_counts(costs, world)
+        fine = sharding.refine_equal_counts(costs, snake)
+        assert sorted(i for r in fine for i in r) == list(range(world * per))
+        assert all(len(r) == per for r in fine)
+        spread = lambda sh: max(sum(costs[i] for i in r) for r in sh) - min(sum(costs[i] for i in r) for r in sh)
+        assert spread(fine) <= spread(snake) + 1e-12
+        if per >= 5:
+            assert spread(fine) < 0.02 * max(costs)
+        assert sharding.refine_equal_counts(costs, snake) == fine          # deterministic
