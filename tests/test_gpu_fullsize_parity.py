@@ -80,7 +80,11 @@ def _b_scale(G, prm, o):
     return float(v.max())
 
 
-@pytest.mark.parametrize("workload,n_obj", [("kitti_batch32", 32), ("redwood_chair", 1), ("kitti_single", 1)])
+# QSP_PARITY_MORE=1 (offline studies, several minutes of CPU oracle): more single-object cases of configs 1 and 3
+_MORE = os.environ.get("QSP_PARITY_MORE", "0") != "0"
+
+
+@pytest.mark.parametrize("workload,n_obj", [("kitti_batch32", 32), ("redwood_chair", 3 if _MORE else 1), ("kitti_single", 6 if _MORE else 1)])
 def test_per_iteration_parity_at_benchmark_size(dev, decoder_state, orc, workload, n_obj):
     from qsp_slam_b200.reconstruct.optimizer import Optimizer
     from qsp_slam_b200.reconstruct.utils import ForceKeyErrorDict
