@@ -541,14 +541,12 @@ def main():
         configs = None
         if not args.no_configs and world == 1:
             configs = other_configs(torch, dev, state, decode, pk)
-        cfgd = workload_config(world, B)
-        cfgd["good_objects"] = good
-        cfgd["shares"] = balance
+        cfgd = workload_config(world, B)                 # identical to the reference arm's `config` (same_config)
         out = {"metric": METRIC, "value": value, "unit": "objects/s",
                "n_gpus": world, "steps": args.steps, "warmup": W,
                "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
                "vs_baseline": None, "dtype": DTYPE, "data": "synthetic",
-               "config": cfgd,
+               "config": cfgd, "good_objects": good, "shares": balance,
                "clocks": clocks, "gpu_launches": int(launches),
                "e2e": {"value": e2e, "unit": "objects/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
                "roofline": roof, "cpu_baseline": cpu, "parity": parity, "configs": configs,
