@@ -88,6 +88,16 @@ k_decoder_p3(TcDecoderDev dw, const float* __restrict__ pts, const int* __restri
           const int nt = tc_step_halves(s) * tc_step_kblocks(s) * 2;
           for (int t = 0; t < nt; ++t) {
             mbar_wait(&empty[stage], ph ^ 1);
+#ifdef QSP_EXPERIMENTAL
+            // timing experiment (QSP_TC_DEBUG bit 0; results are garbage): after the first tile the ring stages keep
+            // the weights they hold - what the L2 -> shared-memory weight stream costs
+            if ((g_tc_dbg & 1) && i > 0) {
+              mbar_arrive(&full[stage]);
+              src += TC_TILE_BYTES;
+              if (++stage == NST) { stage = 0; ph ^= 1; }
+              continue;
+            }
+#endif
             mbar_expect_tx(&full[stage], STAGE_BYTES);
             bulk_g2s(sB + stage * STAGE_BYTES, src, STAGE_BYTES, &full[stage]);
             src += TC_TILE_BYTES;
